@@ -1,0 +1,428 @@
+// partition.cu -- row hashing, hash partitioning and the stable scatter ("Split") kernels.
+//
+// Replaces (reference, relative to cpp/src/cylon/): arrow/arrow_partition_kernels.cpp:67-330 (hash kernels),
+// partition/partition.cpp:27-166 (MapToHashPartitions, Split) and arrow/arrow_kernels.cpp:33-195 (splitters).
+//
+// Design (B200): HBM-bound byte shuffling. One WARP owns a tile of consecutive rows and walks it 32 rows at a
+// time (256 B coalesced key loads, several rounds in flight). Inside a round `match.any` groups the lanes by
+// partition, so a row's stable rank is  cursor[pid] + popc(peers below me)  and one leader lane per group
+// advances the warp-private shared-memory cursor -- no atomics, no inter-warp synchronisation, and the result
+// is deterministic (rows keep their input order inside a partition, like the reference's builders).
+// Pass 1 writes per-tile histograms (partition-major), a device scan turns them into per-tile write cursors,
+// pass 2 recomputes the partition ids (cheaper than storing 4 B/row) and either emits dest[] or scatters every
+// fixed-width column directly. The scattered stores of one warp form <= P short runs that the 126 MB L2 merges
+// into full lines before they reach HBM.
+#include "common.cuh"
+#include "scan.cuh"
+
+namespace cylb {
+
+constexpr int kPartThreads = 256;
+constexpr int kPartWarps = kPartThreads / 32;
+constexpr int kUnroll = 4;  // rounds whose loads are issued together
+
+enum PartMode : int { PM_PID_HIST = 0, PM_TILE_HIST = 1, PM_DEST = 2 };
+
+struct ScatterCols {
+  const uint8_t *src[kMaxCols];
+  uint8_t *dst[kMaxCols];
+  int32_t width[kMaxCols];
+  int32_t n;
+};
+
+struct PartArgs {
+  DCols keys;
+  const uint32_t *pid_in;  // when non-null, partition ids are read instead of hashed
+  const uint64_t *digit_keys;  // when non-null, pid = 8-bit digit of these keys (radix sort pass)
+  int32_t digit_shift;
+  uint32_t *pid_out;       // optional
+  int64_t n;
+  uint32_t P;
+  int32_t pow2;
+  int32_t rounds;  // 32-row rounds per warp tile (multiple of kUnroll)
+  int64_t ntiles;
+  uint32_t *tile_hist;                // [P][ntiles]  (PM_TILE_HIST)
+  const int64_t *tile_base;           // [P][ntiles]  (PM_DEST)
+  int64_t *dest;                      // optional     (PM_DEST)
+  unsigned long long *global_hist;    // [P]          (PM_PID_HIST)
+  ScatterCols sc;                     // optional fused scatter (PM_DEST)
+};
+
+__device__ __forceinline__ uint32_t row_pid(const PartArgs &a, int64_t i) {
+  if (a.digit_keys) return (uint32_t)(a.digit_keys[i] >> a.digit_shift) & 0xFFu;
+  if (a.pid_in) return a.pid_in[i];
+  return ref_partition_of(ref_row_hash(a.keys, i), a.P, a.pow2 != 0);
+}
+
+__device__ __forceinline__ void scatter_one(const ScatterCols &sc, int c, int64_t i, int64_t d) {
+  switch (sc.width[c]) {
+    case 8: reinterpret_cast<uint64_t *>(sc.dst[c])[d] = reinterpret_cast<const uint64_t *>(sc.src[c])[i]; break;
+    case 4: reinterpret_cast<uint32_t *>(sc.dst[c])[d] = reinterpret_cast<const uint32_t *>(sc.src[c])[i]; break;
+    case 16: reinterpret_cast<uint4 *>(sc.dst[c])[d] = reinterpret_cast<const uint4 *>(sc.src[c])[i]; break;
+    case 2: reinterpret_cast<uint16_t *>(sc.dst[c])[d] = reinterpret_cast<const uint16_t *>(sc.src[c])[i]; break;
+    case 1: sc.dst[c][d] = sc.src[c][i]; break;
+    default: {
+      const int w = sc.width[c];
+      const uint8_t *s = sc.src[c] + i * (int64_t)w;
+      uint8_t *t = sc.dst[c] + d * (int64_t)w;
+      for (int b = 0; b < w; b++) t[b] = s[b];
+    }
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kPartThreads) partition_tiles_kernel(const __grid_constant__ PartArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5;
+  const unsigned lane = lane_id();
+  const unsigned lt = lanemask_lt();
+  // warp-private cursors: u32 counts (hist modes) or i64 destinations (dest mode)
+  uint32_t *cnt32 = reinterpret_cast<uint32_t *>(smem_raw) + (size_t)warp * a.P;
+  int64_t *cur64 = reinterpret_cast<int64_t *>(smem_raw) + (size_t)warp * a.P;
+  const int64_t tile_rows = (int64_t)a.rounds * 32;
+  const int64_t warps_total = (int64_t)gridDim.x * kPartWarps;
+
+  if (MODE == PM_PID_HIST) {
+    for (uint32_t p = lane; p < a.P; p += 32) cnt32[p] = 0;
+    __syncwarp();
+  }
+
+  for (int64_t tile = (int64_t)blockIdx.x * kPartWarps + warp; tile < a.ntiles; tile += warps_total) {
+    if (MODE == PM_TILE_HIST) {
+      for (uint32_t p = lane; p < a.P; p += 32) cnt32[p] = 0;
+    } else if (MODE == PM_DEST) {
+      for (uint32_t p = lane; p < a.P; p += 32) cur64[p] = a.tile_base[(int64_t)p * a.ntiles + tile];
+    }
+    __syncwarp();
+    const int64_t start = tile * tile_rows;
+    for (int r0 = 0; r0 < a.rounds; r0 += kUnroll) {
+      uint32_t pid[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; u++) {
+        const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
+        pid[u] = i < a.n ? row_pid(a, i) : 0xFFFFFFFFu;
+      }
+      int64_t d[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; u++) {
+        const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
+        const bool valid = i < a.n;
+        const unsigned peers = __match_any_sync(0xffffffffu, pid[u]);
+        const unsigned rank = __popc(peers & lt);
+        if (MODE == PM_DEST) {
+          d[u] = valid ? cur64[pid[u]] + rank : -1;
+          __syncwarp();
+          if (valid && rank == 0) cur64[pid[u]] += __popc(peers);
+          __syncwarp();
+        } else {
+          if (valid && rank == 0) cnt32[pid[u]] += __popc(peers);
+          __syncwarp();
+          if (MODE == PM_PID_HIST && valid && a.pid_out) a.pid_out[i] = pid[u];
+        }
+      }
+      if (MODE == PM_DEST) {
+        if (a.dest) {
+#pragma unroll
+          for (int u = 0; u < kUnroll; u++) {
+            const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
+            if (d[u] >= 0) a.dest[i] = d[u];
+          }
+        }
+        if (a.pid_out) {
+#pragma unroll
+          for (int u = 0; u < kUnroll; u++) {
+            const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
+            if (d[u] >= 0) a.pid_out[i] = pid[u];
+          }
+        }
+        for (int c = 0; c < a.sc.n; c++) {
+#pragma unroll
+          for (int u = 0; u < kUnroll; u++) {
+            const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
+            if (d[u] >= 0) scatter_one(a.sc, c, i, d[u]);
+          }
+        }
+      }
+    }
+    if (MODE == PM_TILE_HIST) {
+      __syncwarp();
+      for (uint32_t p = lane; p < a.P; p += 32) a.tile_hist[(int64_t)p * a.ntiles + tile] = cnt32[p];
+      __syncwarp();
+    }
+  }
+  if (MODE == PM_PID_HIST) {
+    __syncwarp();
+    for (uint32_t p = lane; p < a.P; p += 32)
+      if (cnt32[p]) atomicAdd(&a.global_hist[p], (unsigned long long)cnt32[p]);
+  }
+}
+
+__global__ void extract_part_offsets(const int64_t *__restrict__ base, int64_t ntiles, uint32_t P, int64_t *__restrict__ part_offsets) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p <= P) part_offsets[p] = base[(int64_t)p * ntiles];
+}
+
+__global__ void row_hash_kernel(const __grid_constant__ DCols keys, int64_t n, uint32_t *__restrict__ h) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) h[i] = ref_row_hash(keys, i);
+}
+
+static int pick_rounds(int64_t n, uint32_t P) {
+  // keep #counters (ntiles * P) well below #rows, and tiles small enough to spread over 148 SMs x 64 warps
+  int rounds = 32;
+  while (rounds < 4096 && (int64_t)rounds * 32 < (int64_t)P * 8) rounds *= 2;
+  (void)n;
+  return rounds;
+}
+
+static int grid_for(int64_t ntiles, int blocks_per_sm) {
+  int64_t want = div_up(ntiles, kPartWarps);
+  int64_t cap = (int64_t)num_sms() * blocks_per_sm;
+  return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
+}
+
+template <int MODE>
+static int launch_part(const PartArgs &a, size_t smem, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (smem > 48 * 1024 && !attr_set) {
+    CYL_CUDA(cudaFuncSetAttribute(partition_tiles_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    attr_set = true;
+  }
+  const int bps = smem > 16 * 1024 ? 2 : 8;
+  partition_tiles_kernel<MODE><<<grid_for(a.ntiles, bps), kPartThreads, smem, stream>>>(a);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+// shared driver: tile histogram -> scan -> dest / fused scatter
+static int partition_map_impl(const DCols *keys, const uint32_t *pid_in, int64_t n, uint32_t P, uint32_t *pid_out, int64_t *dest,
+                              const ScatterCols *sc, int64_t *part_offsets, cudaStream_t stream, const char *who,
+                              const uint64_t *digit_keys = nullptr, int digit_shift = 0) {
+  if (P == 0 || P > 1024) return fail(CYL_Invalid, "%s: num_partitions must be in [1, 1024], got %u", who, P);
+  if (n < 0 || n > 0xFFFFFFFEll) return fail(CYL_CapacityError, "%s: %lld rows (max 2^32-2 per GPU)", who, (long long)n);
+  PartArgs a;
+  memset(&a, 0, sizeof(a));
+  if (keys) a.keys = *keys;
+  a.pid_in = pid_in;
+  a.digit_keys = digit_keys;
+  a.digit_shift = digit_shift;
+  a.pid_out = pid_out;
+  a.n = n;
+  a.P = P;
+  a.pow2 = (P & (P - 1)) == 0;
+  a.rounds = pick_rounds(n, P);
+  a.ntiles = n == 0 ? 0 : div_up(n, (int64_t)a.rounds * 32);
+  if (n == 0) {
+    if (part_offsets) CYL_CUDA(cudaMemsetAsync(part_offsets, 0, (P + 1) * sizeof(int64_t), stream));
+    return CYL_OK;
+  }
+  const int64_t ncounters = a.ntiles * P;
+  Scratch hist, base;
+  CYL_TRY(hist.alloc((size_t)ncounters * sizeof(uint32_t), stream));
+  CYL_TRY(base.alloc((size_t)(ncounters + 1) * sizeof(int64_t), stream));
+  a.tile_hist = hist.as<uint32_t>();
+  CYL_TRY(launch_part<PM_TILE_HIST>(a, (size_t)kPartWarps * P * sizeof(uint32_t), stream));
+  CYL_TRY(exclusive_scan<uint32_t>(hist.as<uint32_t>(), ncounters, base.as<int64_t>(), stream));
+  if (part_offsets) {
+    extract_part_offsets<<<(P + 1 + 255) / 256, 256, 0, stream>>>(base.as<int64_t>(), a.ntiles, P, part_offsets);
+    CYL_LAUNCH_CHECK();
+  }
+  a.tile_base = base.as<int64_t>();
+  a.dest = dest;
+  if (sc) a.sc = *sc;
+  CYL_TRY(launch_part<PM_DEST>(a, (size_t)kPartWarps * P * sizeof(int64_t), stream));
+  return CYL_OK;
+}
+
+// ---- element-wise scatter helpers --------------------------------------------------------------------------
+template <typename T>
+__global__ void scatter_fixed_kernel(const T *__restrict__ src, const int64_t *__restrict__ dest, int64_t n, T *__restrict__ dst) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) dst[dest[i]] = src[i];
+}
+
+__global__ void scatter_bytes_kernel(const uint8_t *__restrict__ src, int32_t w, const int64_t *__restrict__ dest, int64_t n,
+                                     uint8_t *__restrict__ dst) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint8_t *s = src + i * (int64_t)w;
+    uint8_t *t = dst + dest[i] * (int64_t)w;
+    for (int b = 0; b < w; b++) t[b] = s[b];
+  }
+}
+
+__global__ void scatter_lengths_kernel(const int32_t *__restrict__ off, const int64_t *__restrict__ dest, int64_t n,
+                                       int32_t *__restrict__ len_out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    len_out[dest[i]] = off[i + 1] - off[i];
+}
+
+__global__ void narrow_offsets_kernel(const int64_t *__restrict__ in, int64_t n1, int32_t *__restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n1; i += (int64_t)gridDim.x * blockDim.x) out[i] = (int32_t)in[i];
+}
+
+// one warp copies one row's bytes (rows are short strings; lanes stride over the bytes)
+__global__ void scatter_var_bytes_kernel(const int32_t *__restrict__ soff, const uint8_t *__restrict__ sdata,
+                                         const int64_t *__restrict__ dest, int64_t n, const int32_t *__restrict__ doff,
+                                         uint8_t *__restrict__ ddata) {
+  const int64_t gthread = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+  // 4 lanes per row
+  for (int64_t i = gthread >> 2; i < n; i += nthreads >> 2) {
+    const int32_t b = soff[i], len = soff[i + 1] - b;
+    const int32_t o = doff[dest ? dest[i] : i];
+    for (int32_t t = (int32_t)(gthread & 3); t < len; t += 4) ddata[o + t] = sdata[b + t];
+  }
+}
+
+__global__ void scatter_validity_kernel(const uint8_t *__restrict__ vsrc, const int64_t *__restrict__ dest, int64_t n,
+                                        uint32_t *__restrict__ vdst) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (bit_is_set(vsrc, i)) {
+      const int64_t d = dest[i];
+      atomicOr(&vdst[d >> 5], 1u << (d & 31));
+    }
+  }
+}
+
+static inline int ew_grid(int64_t n, int threads = 256) {
+  int64_t b = div_up(n, threads);
+  int64_t cap = (int64_t)num_sms() * 16;
+  return (int)(b < 1 ? 1 : (b < cap ? b : cap));
+}
+
+int scatter_fixed(const void *src, int32_t w, const int64_t *dest, int64_t n, void *dst, cudaStream_t stream) {
+  if (n == 0) return CYL_OK;
+  const int g = ew_grid(n);
+  switch (w) {
+    case 1: scatter_fixed_kernel<uint8_t><<<g, 256, 0, stream>>>((const uint8_t *)src, dest, n, (uint8_t *)dst); break;
+    case 2: scatter_fixed_kernel<uint16_t><<<g, 256, 0, stream>>>((const uint16_t *)src, dest, n, (uint16_t *)dst); break;
+    case 4: scatter_fixed_kernel<uint32_t><<<g, 256, 0, stream>>>((const uint32_t *)src, dest, n, (uint32_t *)dst); break;
+    case 8: scatter_fixed_kernel<uint64_t><<<g, 256, 0, stream>>>((const uint64_t *)src, dest, n, (uint64_t *)dst); break;
+    case 16: scatter_fixed_kernel<uint4><<<g, 256, 0, stream>>>((const uint4 *)src, dest, n, (uint4 *)dst); break;
+    default:
+      if (w <= 0) return fail(CYL_Invalid, "scatter_fixed: byte_width %d", w);
+      scatter_bytes_kernel<<<g, 256, 0, stream>>>((const uint8_t *)src, w, dest, n, (uint8_t *)dst);
+  }
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+// one stable 8-bit LSD radix pass over (u64 key, u32 value) pairs; shares the warp-tile ranking above
+int radix_pass_pairs(const uint64_t *keys_in, const uint32_t *vals_in, uint64_t *keys_out, uint32_t *vals_out, int64_t n, int shift,
+                     cudaStream_t stream) {
+  ScatterCols sc;
+  memset(&sc, 0, sizeof(sc));
+  sc.n = 2;
+  sc.src[0] = reinterpret_cast<const uint8_t *>(keys_in);
+  sc.dst[0] = reinterpret_cast<uint8_t *>(keys_out);
+  sc.width[0] = 8;
+  sc.src[1] = reinterpret_cast<const uint8_t *>(vals_in);
+  sc.dst[1] = reinterpret_cast<uint8_t *>(vals_out);
+  sc.width[1] = 4;
+  return partition_map_impl(nullptr, nullptr, n, 256, nullptr, nullptr, &sc, nullptr, stream, "radix_pass", keys_in, shift);
+}
+
+}  // namespace cylb
+
+using namespace cylb;
+
+extern "C" {
+
+int cyl_row_hash(const cyl_column_t *cols, int32_t ncols, int64_t nrows, uint32_t *h, void *stream) {
+  DCols k;
+  CYL_TRY(make_dcols(cols, ncols, nrows, &k, "cyl_row_hash"));
+  if (nrows == 0) return CYL_OK;
+  row_hash_kernel<<<ew_grid(nrows), 256, 0, (cudaStream_t)stream>>>(k, nrows, h);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_hash_partition(const cyl_column_t *cols, int32_t ncols, int64_t nrows, uint32_t P, uint32_t *pid, uint64_t *hist, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (ncols < 1) return fail(CYL_Invalid, "cyl_hash_partition: needs at least one key column");
+  if (P == 0 || P > 4096) return fail(CYL_Invalid, "cyl_hash_partition: num_partitions must be in [1, 4096], got %u", P);
+  PartArgs a;
+  memset(&a, 0, sizeof(a));
+  CYL_TRY(make_dcols(cols, ncols, nrows, &a.keys, "cyl_hash_partition"));
+  CYL_CUDA(cudaMemsetAsync(hist, 0, P * sizeof(uint64_t), s));
+  if (nrows == 0) return CYL_OK;
+  a.pid_out = pid;
+  a.n = nrows;
+  a.P = P;
+  a.pow2 = (P & (P - 1)) == 0;
+  a.rounds = 32;
+  a.ntiles = div_up(nrows, 32 * 32);
+  a.global_hist = reinterpret_cast<unsigned long long *>(hist);
+  return launch_part<PM_PID_HIST>(a, (size_t)kPartWarps * P * sizeof(uint32_t), s);
+}
+
+int cyl_scatter_map(const uint32_t *pid, int64_t nrows, uint32_t P, int64_t *dest, int64_t *part_offsets, void *stream) {
+  if (nrows > 0 && (!pid || !dest)) return fail(CYL_Invalid, "cyl_scatter_map: null pid/dest");
+  return partition_map_impl(nullptr, pid, nrows, P, nullptr, dest, nullptr, part_offsets, (cudaStream_t)stream, "cyl_scatter_map");
+}
+
+int cyl_partition_map(const cyl_column_t *cols, int32_t ncols, int64_t nrows, uint32_t P, uint32_t *pid_out, int64_t *dest,
+                      int64_t *part_offsets, void *stream) {
+  if (ncols < 1) return fail(CYL_Invalid, "cyl_partition_map: needs at least one key column");
+  DCols k;
+  CYL_TRY(make_dcols(cols, ncols, nrows, &k, "cyl_partition_map"));
+  return partition_map_impl(&k, nullptr, nrows, P, pid_out, dest, nullptr, part_offsets, (cudaStream_t)stream, "cyl_partition_map");
+}
+
+int cyl_scatter_fixed(const void *src, int32_t byte_width, const int64_t *dest, int64_t nrows, void *dst, void *stream) {
+  return scatter_fixed(src, byte_width, dest, nrows, dst, (cudaStream_t)stream);
+}
+
+int cyl_scatter_varwidth(const int32_t *src_offsets, const uint8_t *src_data, const int64_t *dest, int64_t nrows, int32_t *dst_offsets,
+                         uint8_t *dst_data, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (nrows == 0) {
+    CYL_CUDA(cudaMemsetAsync(dst_offsets, 0, sizeof(int32_t), s));
+    return CYL_OK;
+  }
+  Scratch lens, offs64;
+  CYL_TRY(lens.alloc((size_t)nrows * sizeof(int32_t), s));
+  CYL_TRY(offs64.alloc((size_t)(nrows + 1) * sizeof(int64_t), s));
+  scatter_lengths_kernel<<<ew_grid(nrows), 256, 0, s>>>(src_offsets, dest, nrows, lens.as<int32_t>());
+  CYL_LAUNCH_CHECK();
+  CYL_TRY(exclusive_scan<int32_t>(lens.as<int32_t>(), nrows, offs64.as<int64_t>(), s));
+  narrow_offsets_kernel<<<ew_grid(nrows + 1), 256, 0, s>>>(offs64.as<int64_t>(), nrows + 1, dst_offsets);
+  CYL_LAUNCH_CHECK();
+  scatter_var_bytes_kernel<<<ew_grid(nrows * 4), 256, 0, s>>>(src_offsets, src_data, dest, nrows, dst_offsets, dst_data);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_scatter_validity(const uint8_t *vsrc, const int64_t *dest, int64_t nrows, uint8_t *vdst, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  CYL_CUDA(cudaMemsetAsync(vdst, 0, (size_t)div_up(nrows, 32) * 4, s));
+  if (nrows == 0) return CYL_OK;
+  scatter_validity_kernel<<<ew_grid(nrows), 256, 0, s>>>(vsrc, dest, nrows, reinterpret_cast<uint32_t *>(vdst));
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_partition_scatter_fixed(const cyl_column_t *cols, int32_t ncols, const int32_t *key_col_idx, int32_t nkeys, int64_t nrows,
+                                uint32_t P, void *const *dst, int64_t *part_offsets, void *stream) {
+  if (ncols < 1 || ncols > kMaxCols) return fail(CYL_Invalid, "cyl_partition_scatter_fixed: %d columns (1..%d)", ncols, kMaxCols);
+  if (nkeys < 1 || nkeys > ncols) return fail(CYL_Invalid, "cyl_partition_scatter_fixed: %d key columns", nkeys);
+  cyl_column_t kc[kMaxCols];
+  for (int i = 0; i < nkeys; i++) {
+    if (key_col_idx[i] < 0 || key_col_idx[i] >= ncols) return fail(CYL_IndexError, "cyl_partition_scatter_fixed: key column %d out of range", key_col_idx[i]);
+    kc[i] = cols[key_col_idx[i]];
+  }
+  DCols k;
+  CYL_TRY(make_dcols(kc, nkeys, nrows, &k, "cyl_partition_scatter_fixed"));
+  ScatterCols sc;
+  memset(&sc, 0, sizeof(sc));
+  sc.n = ncols;
+  for (int c = 0; c < ncols; c++) {
+    if (cols[c].type == CYL_STRING || cols[c].type == CYL_BINARY || cols[c].byte_width <= 0)
+      return fail(CYL_Invalid, "cyl_partition_scatter_fixed: column %d is not fixed width", c);
+    if (cols[c].length != nrows) return fail(CYL_Invalid, "cyl_partition_scatter_fixed: column %d length mismatch", c);
+    sc.src[c] = static_cast<const uint8_t *>(cols[c].data);
+    sc.dst[c] = static_cast<uint8_t *>(dst[c]);
+    sc.width[c] = cols[c].byte_width;
+  }
+  return partition_map_impl(&k, nullptr, nrows, P, nullptr, nullptr, &sc, part_offsets, (cudaStream_t)stream, "cyl_partition_scatter_fixed");
+}
+
+}  // extern "C"

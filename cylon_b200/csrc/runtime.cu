@@ -1,0 +1,181 @@
+// runtime.cu -- error plumbing, device memory helpers and column validation of the C-ABI.
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace cylb {
+
+static thread_local char g_err[1024] = "";
+
+int fail(int code, const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int cuda_fail(cudaError_t e, const char *expr, const char *file, int line) {
+  const char *base = strrchr(file, '/');
+  snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), base ? base + 1 : file, line, expr);
+  return e == cudaErrorMemoryAllocation ? CYL_OutOfMemory : CYL_ExecutionError;
+}
+
+int Scratch::alloc(size_t bytes, cudaStream_t stream) {
+  release();
+  s = stream;
+  if (bytes == 0) bytes = 16;
+  cudaError_t e = cudaMallocAsync(&p, bytes, stream);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    return cuda_fail(e, "cudaMallocAsync(scratch)", __FILE__, __LINE__);
+  }
+  return CYL_OK;
+}
+
+void Scratch::release() {
+  if (p) {
+    cudaFreeAsync(p, s);
+    p = nullptr;
+  }
+}
+
+int num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+int make_dcols(const cyl_column_t *cols, int32_t ncols, int64_t nrows, DCols *out, const char *who) {
+  if (ncols < 0 || ncols > kMaxCols) return fail(CYL_Invalid, "%s: %d columns (max %d)", who, ncols, kMaxCols);
+  if (ncols > 0 && cols == nullptr) return fail(CYL_Invalid, "%s: null column array", who);
+  if (nrows < 0 || nrows > 0xFFFFFFFEll) return fail(CYL_CapacityError, "%s: %lld rows (max 2^32-2 per GPU)", who, (long long)nrows);
+  memset(out, 0, sizeof(*out));
+  out->n = ncols;
+  for (int c = 0; c < ncols; c++) {
+    const cyl_column_t &s = cols[c];
+    DCol &d = out->c[c];
+    d.kind = hash_kind_of(s.type);
+    if (d.kind == HK_UNSUPPORTED)
+      return fail(CYL_ExecutionError, "%s: column %d has unsupported type id %d", who, c, s.type);  // partition.cpp:102-104
+    if (s.length != nrows) return fail(CYL_Invalid, "%s: column %d has %lld rows, expected %lld", who, c, (long long)s.length, (long long)nrows);
+    if (d.kind == HK_MURMUR_VAR) {
+      if (nrows > 0 && s.offsets == nullptr) return fail(CYL_Invalid, "%s: column %d is variable width but has no offsets", who, c);
+      d.width = 0;
+    } else {
+      d.width = s.byte_width;
+      if (d.kind == HK_MODULO || s.type == CYL_FLOAT || s.type == CYL_DOUBLE) {
+        int want = 0;
+        switch (s.type) {
+          case CYL_UINT8: case CYL_INT8: want = 1; break;
+          case CYL_UINT16: case CYL_INT16: want = 2; break;
+          case CYL_UINT32: case CYL_INT32: case CYL_FLOAT: case CYL_DATE32: case CYL_TIME32: want = 4; break;
+          default: want = 8; break;
+        }
+        if (d.width != want) return fail(CYL_Invalid, "%s: column %d type %d needs byte_width %d, got %d", who, c, s.type, want, d.width);
+      } else if (d.width <= 0) {
+        return fail(CYL_Invalid, "%s: column %d fixed-size binary needs byte_width > 0", who, c);
+      }
+    }
+    if (nrows > 0 && s.data == nullptr && d.kind != HK_MURMUR_VAR) return fail(CYL_Invalid, "%s: column %d has no data", who, c);
+    d.data = static_cast<const uint8_t *>(s.data);
+    d.offsets = s.offsets;
+    d.validity = s.validity;
+    d.type = s.type;
+    d.is_signed = type_is_signed(s.type) ? 1 : 0;
+  }
+  return CYL_OK;
+}
+
+bool is_exact_key(const DCols &k) {
+  return k.n == 1 && k.c[0].kind != HK_MURMUR_VAR && k.c[0].width <= 8 && k.c[0].type != CYL_FIXED_SIZE_BINARY;
+}
+
+}  // namespace cylb
+
+using namespace cylb;
+
+extern "C" {
+
+int cyl_version(void) { return 100; }
+
+const char *cyl_last_error(void) { return g_err; }
+
+int cyl_init(int32_t device) {
+  CYL_CUDA(cudaSetDevice(device));
+  cudaMemPool_t pool;
+  CYL_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+  uint64_t threshold = UINT64_MAX;  // keep freed scratch in the pool: no cudaMalloc/cudaFree on the hot path
+  CYL_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+  return CYL_OK;
+}
+
+int cyl_device_count(int32_t *count) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    *count = 0;
+    return cuda_fail(e, "cudaGetDeviceCount", __FILE__, __LINE__);
+  }
+  *count = n;
+  return CYL_OK;
+}
+
+int cyl_malloc(void **ptr, int64_t bytes) {
+  if (bytes < 0) return fail(CYL_Invalid, "cyl_malloc: negative size");
+  *ptr = nullptr;
+  CYL_CUDA(cudaMalloc(ptr, bytes == 0 ? 16 : (size_t)bytes));
+  return CYL_OK;
+}
+
+int cyl_free(void *ptr) {
+  if (ptr) CYL_CUDA(cudaFree(ptr));
+  return CYL_OK;
+}
+
+int cyl_memset(void *ptr, int32_t value, int64_t bytes, void *stream) {
+  if (bytes > 0) CYL_CUDA(cudaMemsetAsync(ptr, value, (size_t)bytes, (cudaStream_t)stream));
+  return CYL_OK;
+}
+
+int cyl_memcpy_h2d(void *dst, const void *src, int64_t bytes, void *stream) {
+  if (bytes > 0) CYL_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return CYL_OK;
+}
+
+int cyl_memcpy_d2h(void *dst, const void *src, int64_t bytes, void *stream) {
+  if (bytes > 0) CYL_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return CYL_OK;
+}
+
+int cyl_memcpy_d2d(void *dst, const void *src, int64_t bytes, void *stream) {
+  if (bytes > 0) CYL_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return CYL_OK;
+}
+
+int cyl_stream_sync(void *stream) {
+  CYL_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return CYL_OK;
+}
+
+int cyl_host_alloc_pinned(void **ptr, int64_t bytes) {
+  *ptr = nullptr;
+  CYL_CUDA(cudaHostAlloc(ptr, bytes <= 0 ? 16 : (size_t)bytes, cudaHostAllocDefault));
+  return CYL_OK;
+}
+
+int cyl_host_free_pinned(void *ptr) {
+  if (ptr) CYL_CUDA(cudaFreeHost(ptr));
+  return CYL_OK;
+}
+
+}  // extern "C"

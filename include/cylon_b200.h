@@ -1,0 +1,135 @@
+/*
+ * cylon_b200.h -- C-ABI of libcylon_b200.so: the B200 (sm_100a) kernels behind Cylon's distributed
+ * relational hot path (hash-partition -> shuffle -> local join | group-by | set operation).
+ *
+ * Conventions
+ *   - plain C, no C++/torch types. Every pointer is a DEVICE pointer unless a comment says "host".
+ *   - sizes and row indices are int64_t. A table may hold at most 2^32-2 rows per GPU.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream). Calls are
+ *     asynchronous on that stream unless they return a host value (documented per call).
+ *   - every call returns a cylon::Code (cyl_code_t; 0 = OK), the convention of cpp/src/cylon/status.hpp:21-63.
+ *     cyl_last_error() gives the message of the calling thread's last failure.
+ *   - scratch memory is taken from the device's stream-ordered pool (cudaMallocAsync) and returned before
+ *     the call ends (stream-ordered).
+ *   - citations are relative to /root/reference/cpp/src/cylon/ and name the reference code each entry
+ *     point replaces.
+ */
+#ifndef CYLON_B200_H_
+#define CYLON_B200_H_
+
+#include "cylon_b200_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------- runtime ---------------------- */
+int cyl_version(void);
+const char *cyl_last_error(void); /* host string, valid until the thread's next failing call */
+/* Selects `device` for the calling thread and lets the default memory pool keep freed blocks.
+ * (The reference's counterpart is CylonContext::Init, ctx/cylon_context.cpp:24-30 -- host only.) */
+int cyl_init(int32_t device);
+int cyl_device_count(int32_t *count /* host */);
+int cyl_malloc(void **ptr /* host out */, int64_t bytes);
+int cyl_free(void *ptr);
+int cyl_memset(void *ptr, int32_t value, int64_t bytes, void *stream);
+int cyl_memcpy_h2d(void *dst, const void *src_host, int64_t bytes, void *stream);
+int cyl_memcpy_d2h(void *dst_host, const void *src, int64_t bytes, void *stream);
+int cyl_memcpy_d2d(void *dst, const void *src, int64_t bytes, void *stream);
+int cyl_stream_sync(void *stream);
+int cyl_host_alloc_pinned(void **ptr /* host out */, int64_t bytes);
+int cyl_host_free_pinned(void *ptr);
+
+/* ---------------------------------------------------------------- A: row hashing / partition --- */
+/* h[i] = chain over `cols` of 31*h + colhash(v), h0 = 0: ints/temporal (uint32_t)v, float/double/fixed
+ * binary/string murmur3_x86_32(bytes, seed 0). Validity ignored.
+ * Replaces HashPartitionKernel::UpdateHash (arrow/arrow_partition_kernels.cpp:95-109,151-168,216-240,
+ * 285-304) and TableRowIndexHash (arrow/arrow_comparator.cpp:396-440). */
+int cyl_row_hash(const cyl_column_t *cols /* host array */, int32_t ncols, int64_t nrows, uint32_t *h, void *stream);
+
+/* pid[i] = part(row_hash(i)), part = h & (P-1) if P is a power of two else h % P; hist[p] = #rows.
+ * pid may be NULL (histogram only). hist is uint64[P], overwritten.
+ * Replaces MapToHashPartitions (partition/partition.cpp:92-166) + HashPartitionKernel::Partition
+ * (arrow/arrow_partition_kernels.cpp:71-93,124-149,189-214,258-283). */
+int cyl_hash_partition(const cyl_column_t *cols /* host array */, int32_t ncols, int64_t nrows, uint32_t num_partitions,
+                       uint32_t *pid, uint64_t *hist, void *stream);
+
+/* ---------------------------------------------------------------- B: split (stable scatter) ---- */
+/* dest[i] = part_offsets[pid[i]] + #{j < i : pid[j] == pid[i]}  (row order inside a partition = input order),
+ * part_offsets = exclusive scan of the histogram, int64[P+1]. num_partitions <= 1024.
+ * Replaces the row routing of ArrowArraySplitKernel::Split (arrow/arrow_kernels.cpp:40-72). */
+int cyl_scatter_map(const uint32_t *pid, int64_t nrows, uint32_t num_partitions, int64_t *dest, int64_t *part_offsets,
+                    void *stream);
+/* Same, with pid computed on the fly from the key columns (fuses cyl_hash_partition + cyl_scatter_map;
+ * pid_out may be NULL). */
+int cyl_partition_map(const cyl_column_t *cols /* host array */, int32_t ncols, int64_t nrows, uint32_t num_partitions,
+                      uint32_t *pid_out, int64_t *dest, int64_t *part_offsets, void *stream);
+/* dst[dest[i]] = src[i] for a fixed-width column (numeric: arrow_kernels.cpp:33-72, fixed binary :74-113). */
+int cyl_scatter_fixed(const void *src, int32_t byte_width, const int64_t *dest, int64_t nrows, void *dst, void *stream);
+/* Variable-width column (arrow_kernels.cpp:115-157): dst_offsets (int32[nrows+1], starts at 0) and dst_data
+ * (same byte count as the source) receive the rows in dest order. */
+int cyl_scatter_varwidth(const int32_t *src_offsets, const uint8_t *src_data, const int64_t *dest, int64_t nrows,
+                         int32_t *dst_offsets, uint8_t *dst_data, void *stream);
+/* Validity bitmap: bit dest[i] of vdst = bit i of vsrc. vdst has ceil(nrows/32)*4 bytes, overwritten.
+ * (The reference drops validity in Split -- SURVEY.md B2; this library keeps it.) */
+int cyl_scatter_validity(const uint8_t *vsrc, const int64_t *dest, int64_t nrows, uint8_t *vdst, void *stream);
+/* One fused pass for a table whose columns are all fixed width (1/2/4/8/16 bytes): partition ids from the key
+ * columns, stable destinations and the scatter of every column, without materialising pid or dest.
+ * dst[c] must hold nrows values. part_offsets: int64[P+1] (device). key_col_idx: host array of indices into cols. */
+int cyl_partition_scatter_fixed(const cyl_column_t *cols /* host array */, int32_t ncols, const int32_t *key_col_idx /* host */,
+                                int32_t nkeys, int64_t nrows, uint32_t num_partitions, void *const *dst /* host array of device ptrs */,
+                                int64_t *part_offsets, void *stream);
+
+/* ---------------------------------------------------------------- scan ------------------------- */
+/* out[i] = sum_{j<i} in[j]; out has n+1 entries (out[n] = total). In place (out == in) is NOT allowed. */
+int cyl_exclusive_scan_i64(const int64_t *in, int64_t n, int64_t *out, void *stream);
+
+/* ---------------------------------------------------------------- D: joins --------------------- */
+typedef struct cyl_join_plan cyl_join_plan_t; /* opaque, host object owning device state */
+
+/* Pass 1 of the hash join: build an open-addressing table in HBM over the build side (LEFT -> right table,
+ * RIGHT -> left table, INNER/FULL_OUTER -> the smaller, ties left: join/hash_join.cpp:207-232), probe it and
+ * count the output rows. *num_rows (host) receives M; the call synchronises the stream.
+ * Replaces ArrayIndexHashJoin (join/hash_join.cpp:188-307) and multi_index_hash_join (:92-186). */
+int cyl_hash_join_count(const cyl_column_t *lkeys /* host array */, const cyl_column_t *rkeys /* host array */, int32_t nkeys,
+                        int64_t nl, int64_t nr, int32_t join_type, cyl_join_plan_t **plan /* host out */,
+                        int64_t *num_rows /* host out */, void *stream);
+/* Pass 1 of the sort join: LSD radix argsort of both sides on the key tuple, then per-left-row match ranges
+ * in the sorted right side. Replaces SortJoin (join/sort_join.cpp:36-190,214-370,396-556) and its sorters
+ * (arrow/arrow_kernels.cpp:294-339,386-457; util/sort.hpp:126-145). Never mutates the key columns (D6). */
+int cyl_sort_join_count(const cyl_column_t *lkeys /* host array */, const cyl_column_t *rkeys /* host array */, int32_t nkeys,
+                        int64_t nl, int64_t nr, int32_t join_type, cyl_join_plan_t **plan /* host out */,
+                        int64_t *num_rows /* host out */, void *stream);
+/* Pass 2 (either algorithm): write the M (left row, right row) index pairs, -1 = no partner
+ * (probe_hash_map_no_fill/_with_fill/_outer, join/hash_join.cpp:21-90). Order is unspecified. Frees the plan. */
+int cyl_join_materialize(cyl_join_plan_t *plan, int64_t *l_idx, int64_t *r_idx, void *stream);
+void cyl_join_plan_free(cyl_join_plan_t *plan);
+
+/* ---------------------------------------------------------------- D4: gather ------------------- */
+/* dst[i] = idx[i] < 0 ? 0 : src[idx[i]]; dst_validity (may be NULL) gets bit i = (idx[i] >= 0), it has
+ * ceil(m/32)*4 bytes. Source validity is not propagated, as in the reference.
+ * Replaces copy_array_by_indices (util/copy_arrray.cpp:24-50,87-110,142-292). */
+int cyl_gather_fixed(const void *src, int32_t byte_width, const int64_t *idx, int64_t m, void *dst, uint8_t *dst_validity,
+                     void *stream);
+/* Variable width (util/copy_arrray.cpp:52-85), two steps: offsets (returns total bytes on the host; synchronises),
+ * then bytes into a buffer of that size. */
+int cyl_gather_varwidth_offsets(const int32_t *src_offsets, const int64_t *idx, int64_t m, int32_t *dst_offsets,
+                                int64_t *total_bytes /* host out */, void *stream);
+int cyl_gather_varwidth_data(const int32_t *src_offsets, const uint8_t *src_data, const int64_t *idx, int64_t m,
+                             const int32_t *dst_offsets, uint8_t *dst_data, void *stream);
+/* validity bitmap of a gather by idx: bit i = (idx[i] >= 0); ceil(m/32)*4 bytes (copy_arrray.cpp:39-41,67-68). */
+int cyl_index_validity(const int64_t *idx, int64_t m, uint8_t *validity, void *stream);
+/* number of negative entries (= nulls a gather by idx produces). Host out; synchronises. */
+int cyl_count_negative(const int64_t *idx, int64_t m, int64_t *count /* host out */, void *stream);
+
+/* ---------------------------------------------------------------- checks ----------------------- */
+/* Order-independent checksum of a table: sum over rows of a 64-bit mix of the row's values (nulls count as
+ * zero bits + validity 0). No counterpart in the reference; it is how full-size results are compared with the
+ * CPU oracle without sorting. *checksum is a host out; synchronises. */
+int cyl_table_checksum(const cyl_column_t *cols /* host array */, int32_t ncols, int64_t nrows, uint64_t *checksum /* host out */,
+                       void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CYLON_B200_H_ */
