@@ -282,3 +282,46 @@ def table_checksum(cols, stream=None):
     check(lib().cyl_table_checksum(c_columns(cols), len(cols), C.c_int64(cols[0].length if cols else 0), C.byref(cs),
                                    C.c_void_p(stream)))
     return cs.value
+
+
+def groupby_hash_device(keys, stream=None):
+    n = keys[0].length
+    gid = DeviceBuffer(8 * max(1, n))
+    first = DeviceBuffer(max(1, n))
+    g = C.c_int64()
+    check(lib().cyl_groupby_hash(c_columns(keys), len(keys), C.c_int64(n), _p(gid), _p(first), C.byref(g),
+                                 C.c_void_p(stream)))
+    return gid, first, g.value
+
+
+def groupby_hash(keys, stream=None):
+    gid, first, g = groupby_hash_device(keys, stream)
+    n = keys[0].length
+    return gid.to_numpy(np.int64, n), first.to_numpy(np.uint8, n), g
+
+
+def aggregate(col, gid_buf, num_groups, op, stream=None):
+    dt = np.dtype("int64") if op == COUNT else TYPE2NP[col.type]
+    out = DeviceBuffer(max(1, num_groups) * dt.itemsize)
+    cs = col.c_struct()
+    check(lib().cyl_aggregate(C.byref(cs), _p(gid_buf), C.c_int64(num_groups), C.c_int32(op), _p(out), C.c_void_p(stream)))
+    return out.to_numpy(dt, num_groups)
+
+
+def rowset_mask(lcols, rcols, op, stream=None):
+    nl = lcols[0].length
+    nr = rcols[0].length if rcols else 0
+    ml, mr = DeviceBuffer(max(1, nl)), DeviceBuffer(max(1, nr))
+    check(lib().cyl_rowset_mask(c_columns(lcols), c_columns(rcols if rcols else lcols), len(lcols), C.c_int64(nl),
+                                C.c_int64(nr), C.c_int32(op), _p(ml), _p(mr), C.c_void_p(stream)))
+    return ml.to_numpy(np.uint8, nl), mr.to_numpy(np.uint8, nr)
+
+
+def mask_to_indices(mask, stream=None):
+    mask = np.ascontiguousarray(mask, dtype=np.uint8)
+    n = len(mask)
+    mb = DeviceBuffer.from_numpy(mask)
+    idx = DeviceBuffer(8 * max(1, n))
+    cnt = C.c_int64()
+    check(lib().cyl_mask_to_indices(_p(mb), C.c_int64(n), _p(idx), C.byref(cnt), C.c_void_p(stream)))
+    return idx.to_numpy(np.int64, cnt.value)

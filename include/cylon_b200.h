@@ -122,6 +122,36 @@ int cyl_index_validity(const int64_t *idx, int64_t m, uint8_t *validity, void *s
 /* number of negative entries (= nulls a gather by idx produces). Host out; synchronises. */
 int cyl_count_negative(const int64_t *idx, int64_t m, int64_t *count /* host out */, void *stream);
 
+/* validity of a filter/take that keeps the source's nulls: bit i = idx[i] >= 0 && (vsrc == NULL || bit idx[i] of vsrc).
+ * (arrow::compute::Filter as called at table.cpp:567,586,652,710,968 keeps nulls.) */
+int cyl_gather_validity(const uint8_t *vsrc, const int64_t *idx, int64_t m, uint8_t *vdst, void *stream);
+
+/* ---------------------------------------------------------------- G: group-by ------------------ */
+/* gid[i] = dense id of row i's key tuple, numbered in first-seen order; first_mask[i] = 1 for the first row of each
+ * group (one byte per row); *num_groups is a host out (the call synchronises).
+ * Replaces make_groups (groupby/hash_groupby.cpp:92-126). */
+int cyl_groupby_hash(const cyl_column_t *keys /* host array */, int32_t nkeys, int64_t nrows, int64_t *gid, uint8_t *first_mask,
+                     int64_t *num_groups /* host out */, void *stream);
+/* out[g] = op over { col[i] : gid[i] == g }. out holds num_groups values of the column's type (SUM/MIN/MAX) or int64
+ * (COUNT). SUM wraps in the column's C type, MIN starts at numeric_limits<T>::max(), MAX at numeric_limits<T>::min()
+ * (DBL_MIN/FLT_MIN for floating point -- the reference's behaviour). col is a host pointer to one descriptor.
+ * Replaces aggregate<op,T> (groupby/hash_groupby.cpp:142-201) + compute/aggregate_kernels.hpp:410-485. */
+int cyl_aggregate(const cyl_column_t *col /* host */, const int64_t *gid, int64_t num_groups, int32_t op, void *out, void *stream);
+
+/* ---------------------------------------------------------------- E: set operations / unique --- */
+/* One byte per row: mask_l[i] / mask_r[j] = 1 when the row belongs to the result.
+ *   UNION:     first occurrence of every distinct left row, plus first occurrence of right rows not on the left
+ *   SUBTRACT:  first occurrence of distinct left rows that do not occur on the right   (mask_r zeroed)
+ *   INTERSECT: first occurrence of distinct left rows that also occur on the right     (mask_r zeroed)
+ *   UNIQUE:    first occurrence of every distinct key tuple of `lcols` (rcols/nr/mask_r ignored)
+ * Row equality = per-column value equality over the given columns.
+ * Replaces Union/Subtract/Intersect/Unique (table.cpp:531-721,923-982) up to their Filter calls. */
+int cyl_rowset_mask(const cyl_column_t *lcols /* host array */, const cyl_column_t *rcols /* host array */, int32_t ncols, int64_t nl,
+                    int64_t nr, int32_t op, uint8_t *mask_l, uint8_t *mask_r, void *stream);
+/* idx = ascending positions of the non-zero bytes of mask (a stream compaction; feed it to the gather calls).
+ * idx must hold n entries; *count is a host out (synchronises). Replaces arrow::compute::Filter's selection. */
+int cyl_mask_to_indices(const uint8_t *mask, int64_t n, int64_t *idx, int64_t *count /* host out */, void *stream);
+
 /* ---------------------------------------------------------------- checks ----------------------- */
 /* Order-independent checksum of a table: sum over rows of a 64-bit mix of the row's values (nulls count as
  * zero bits + validity 0). No counterpart in the reference; it is how full-size results are compared with the
