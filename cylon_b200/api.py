@@ -1,0 +1,282 @@
+"""Python mirror of the Cylon table API over the C facade (include/cylon_b200_api.h).
+
+Same operator names and argument meaning as pycylon's Table (python/pycylon/data/table.pyx:314-380,538,642,714,757):
+join / distributed_join, union / subtract / intersect and their distributed_ forms, unique, shuffle, groupby.
+Tables live in HBM; every call goes through the C++ host layer in libcylon_b200.so -- there is no Python or CPU
+compute path here, and a missing library raises.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import (BINARY, COUNT, DOUBLE, FIXED_SIZE_BINARY, FLOAT, FULL_OUTER, HASH, INNER, INTERSECT, LEFT, MAX, MIN, RIGHT,  # noqa: F401
+                   SORT, STRING, SUBTRACT, SUM, UNION, CylColumn, CylonError, check, lib)
+
+_JOIN_TYPES = {"inner": INNER, "left": LEFT, "right": RIGHT, "outer": FULL_OUTER, "fullouter": FULL_OUTER, "full_outer": FULL_OUTER}
+_ALGOS = {"sort": SORT, "hash": HASH}
+_AGGS = {"sum": SUM, "min": MIN, "max": MAX, "count": COUNT}
+
+
+def nccl_unique_id():
+    buf = C.create_string_buffer(128)
+    check(lib().cylon_nccl_unique_id(buf))
+    return buf.raw
+
+
+class CylonContext:
+    """CylonContext(config=None, distributed=False) of pycylon; distributed contexts take the NCCL bootstrap."""
+
+    def __init__(self, device=0, distributed=False, rank=0, world_size=1, nccl_id=None):
+        self._h = C.c_void_p()
+        if distributed:
+            if nccl_id is None or len(nccl_id) != 128:
+                raise ValueError("distributed context needs the 128-byte NCCL unique id created on rank 0")
+            check(lib().cylon_context_init_distributed(C.c_int32(rank), C.c_int32(world_size), C.c_int32(device),
+                                                       C.c_char_p(nccl_id), C.byref(self._h)))
+        else:
+            check(lib().cylon_context_init(C.c_int32(device), C.byref(self._h)))
+
+    def set_stream(self, cuda_stream):
+        check(lib().cylon_context_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def get_rank(self):
+        return lib().cylon_context_rank(self._h)
+
+    def get_world_size(self):
+        return lib().cylon_context_world_size(self._h)
+
+    def barrier(self):
+        check(lib().cylon_context_barrier(self._h))
+
+    def finalize(self):
+        if self._h:
+            lib().cylon_context_finalize(self._h)
+            self._h = None
+
+
+def _host_column(values, type_id=None, validity=None):
+    """-> (CylColumn with host pointers, keepalive list)"""
+    keep = []
+    s = CylColumn()
+    if isinstance(values, np.ndarray) and values.dtype.kind in "iuf":
+        a = np.ascontiguousarray(values)
+        keep.append(a)
+        s.type = type_id if type_id is not None else capi.NP2TYPE[a.dtype]
+        s.byte_width = a.dtype.itemsize
+        s.length = len(a)
+        s.data = a.ctypes.data if a.size else None
+        if a.size == 0:
+            z = np.zeros(1, dtype=a.dtype)
+            keep.append(z)
+            s.data = z.ctypes.data
+    elif isinstance(values, tuple):  # (offsets int32, bytes uint8) -- Arrow string layout
+        offs = np.ascontiguousarray(values[0], dtype=np.int32)
+        data = np.ascontiguousarray(values[1], dtype=np.uint8)
+        if data.size == 0:
+            data = np.zeros(1, dtype=np.uint8)
+        keep += [offs, data]
+        s.type = type_id if type_id is not None else STRING
+        s.byte_width = 0
+        s.length = len(offs) - 1
+        s.offsets = offs.ctypes.data
+        s.data = data.ctypes.data
+    else:
+        vals = [x.encode() if isinstance(x, str) else bytes(x) for x in values]
+        offs = np.zeros(len(vals) + 1, dtype=np.int32)
+        if vals:
+            offs[1:] = np.cumsum([len(x) for x in vals])
+        data = np.frombuffer(b"".join(vals) or b"\0", dtype=np.uint8).copy()
+        keep += [offs, data]
+        s.type = type_id if type_id is not None else STRING
+        s.byte_width = 0
+        s.length = len(vals)
+        s.offsets = offs.ctypes.data
+        s.data = data.ctypes.data
+    if validity is not None:
+        bits = np.packbits(np.asarray(validity, dtype=bool), bitorder="little")
+        bits = np.concatenate([bits, np.zeros(8, dtype=np.uint8)])
+        keep.append(bits)
+        s.validity = bits.ctypes.data
+        s.null_count = int(len(validity) - np.count_nonzero(validity))
+    return s, keep
+
+
+class Table:
+    def __init__(self, handle, ctx):
+        self._h = handle
+        self.ctx = ctx
+
+    # ------------------------------------------------------------------ construction / inspection
+    @classmethod
+    def from_numpy(cls, ctx, columns, names=None, types=None, validity=None):
+        """columns: list of numeric ndarrays / lists of str|bytes / (offsets, bytes) tuples. Copies host -> HBM."""
+        n = len(columns)
+        arr = (CylColumn * max(1, n))()
+        keep = []
+        for i, col in enumerate(columns):
+            s, k = _host_column(col, None if types is None else types[i], None if validity is None else validity[i])
+            arr[i] = s
+            keep.append(k)
+        cnames = None
+        if names is not None:
+            cnames = (C.c_char_p * n)(*[str(x).encode() for x in names])
+        h = C.c_void_p()
+        check(lib().cylon_table_from_host(ctx._h, arr, cnames, C.c_int32(n), C.byref(h)))
+        capi.sync(None)
+        return cls(h, ctx)
+
+    @classmethod
+    def from_device(cls, ctx, dcols, names=None):
+        """Zero-copy view over capi.DCol device columns (they must outlive the table)."""
+        n = len(dcols)
+        arr = capi.c_columns(dcols)
+        cnames = None
+        if names is not None:
+            cnames = (C.c_char_p * n)(*[str(x).encode() for x in names])
+        h = C.c_void_p()
+        check(lib().cylon_table_from_device(ctx._h, arr, cnames, C.c_int32(n), C.byref(h)))
+        t = cls(h, ctx)
+        t._keep = dcols
+        return t
+
+    @property
+    def row_count(self):
+        lib().cylon_table_rows.restype = C.c_int64
+        return lib().cylon_table_rows(self._h)
+
+    @property
+    def column_count(self):
+        return lib().cylon_table_columns(self._h)
+
+    @property
+    def column_names(self):
+        lib().cylon_table_column_name.restype = C.c_char_p
+        return [lib().cylon_table_column_name(self._h, C.c_int32(i)).decode() for i in range(self.column_count)]
+
+    def column_desc(self, i):
+        d = CylColumn()
+        nbytes = C.c_int64()
+        check(lib().cylon_table_column(self._h, C.c_int32(i), C.byref(d), C.byref(nbytes)))
+        return d, nbytes.value
+
+    def to_host(self):
+        """-> list of dicts {type, byte_width, data, offsets, valid, name} (numpy; device -> host copies)."""
+        out = []
+        names = self.column_names
+        for i in range(self.column_count):
+            d, nbytes = self.column_desc(i)
+            n = d.length
+            offs = None
+            if d.type in (STRING, BINARY):
+                data = np.zeros(max(1, nbytes), dtype=np.uint8)
+                offs = np.zeros(n + 1, dtype=np.int32)
+            elif d.type == FIXED_SIZE_BINARY:
+                data = np.zeros(max(1, nbytes), dtype=np.uint8)
+            else:
+                data = np.zeros(max(1, n), dtype=capi.TYPE2NP[d.type])
+            vbits = np.zeros((n + 7) // 8 + 8, dtype=np.uint8) if d.validity else None
+            check(lib().cylon_table_column_to_host(self._h, C.c_int32(i), C.c_void_p(data.ctypes.data),
+                                                   C.c_void_p(offs.ctypes.data) if offs is not None else None,
+                                                   C.c_void_p(vbits.ctypes.data) if vbits is not None else None))
+            valid = None
+            if vbits is not None:
+                valid = np.unpackbits(vbits, bitorder="little")[:n].astype(bool)
+            if d.type in (STRING, BINARY, FIXED_SIZE_BINARY):
+                data = data[:nbytes]
+            else:
+                data = data[:n]
+            out.append({"type": d.type, "byte_width": d.byte_width, "data": data, "offsets": offs, "valid": valid, "name": names[i]})
+        return out
+
+    def checksum(self):
+        cs = C.c_uint64()
+        check(lib().cylon_table_checksum(self._h, C.byref(cs)))
+        return cs.value
+
+    def retain_memory(self, retain):
+        check(lib().cylon_table_retain_memory(self._h, C.c_int32(1 if retain else 0)))
+
+    def free(self):
+        if self._h:
+            lib().cylon_table_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ operators
+    def _join(self, table, join_type, algorithm, left_on, right_on, left_prefix, right_prefix, distributed):
+        jt = _JOIN_TYPES[join_type] if isinstance(join_type, str) else int(join_type)
+        al = _ALGOS[algorithm] if isinstance(algorithm, str) else int(algorithm)
+        lo = (C.c_int32 * len(left_on))(*left_on)
+        ro = (C.c_int32 * len(right_on))(*right_on)
+        h = C.c_void_p()
+        check(lib().cylon_join(self._h, table._h, C.c_int32(jt), C.c_int32(al), lo, ro, C.c_int32(len(left_on)),
+                               left_prefix.encode(), right_prefix.encode(), C.c_int32(1 if distributed else 0), C.byref(h)))
+        return Table(h, self.ctx)
+
+    def join(self, table, join_type="inner", algorithm="sort", left_on=(0,), right_on=(0,), left_prefix="", right_prefix=""):
+        return self._join(table, join_type, algorithm, list(left_on), list(right_on), left_prefix, right_prefix, False)
+
+    def distributed_join(self, table, join_type="inner", algorithm="sort", left_on=(0,), right_on=(0,), left_prefix="", right_prefix=""):
+        return self._join(table, join_type, algorithm, list(left_on), list(right_on), left_prefix, right_prefix, True)
+
+    def _setop(self, table, op, distributed):
+        h = C.c_void_p()
+        check(lib().cylon_set_operation(self._h, table._h, C.c_int32(op), C.c_int32(1 if distributed else 0), C.byref(h)))
+        return Table(h, self.ctx)
+
+    def union(self, table):
+        return self._setop(table, UNION, False)
+
+    def subtract(self, table):
+        return self._setop(table, SUBTRACT, False)
+
+    def intersect(self, table):
+        return self._setop(table, INTERSECT, False)
+
+    def distributed_union(self, table):
+        return self._setop(table, UNION, True)
+
+    def distributed_subtract(self, table):
+        return self._setop(table, SUBTRACT, True)
+
+    def distributed_intersect(self, table):
+        return self._setop(table, INTERSECT, True)
+
+    def unique(self, columns, distributed=False):
+        cols = (C.c_int32 * len(columns))(*columns)
+        h = C.c_void_p()
+        check(lib().cylon_unique(self._h, cols, C.c_int32(len(columns)), C.c_int32(1 if distributed else 0), C.byref(h)))
+        return Table(h, self.ctx)
+
+    def distributed_unique(self, columns):
+        return self.unique(columns, True)
+
+    def shuffle(self, hash_columns):
+        cols = (C.c_int32 * len(hash_columns))(*hash_columns)
+        h = C.c_void_p()
+        check(lib().cylon_shuffle(self._h, cols, C.c_int32(len(hash_columns)), C.byref(h)))
+        return Table(h, self.ctx)
+
+    def hash_partition(self, hash_columns, num_partitions):
+        cols = (C.c_int32 * len(hash_columns))(*hash_columns)
+        outs = (C.c_void_p * num_partitions)()
+        check(lib().cylon_hash_partition(self._h, cols, C.c_int32(len(hash_columns)), C.c_int32(num_partitions), outs))
+        return [Table(C.c_void_p(outs[p]), self.ctx) for p in range(num_partitions)]
+
+    def groupby(self, index, agg_cols, agg_ops, distributed=False):
+        """DistributedHashGroupBy(table, index_cols, aggregate_cols, aggregate_ops) when distributed, else HashGroupBy."""
+        index = [index] if isinstance(index, int) else list(index)
+        ops = [_AGGS[o] if isinstance(o, str) else int(o) for o in agg_ops]
+        ic = (C.c_int32 * len(index))(*index)
+        ac = (C.c_int32 * len(agg_cols))(*agg_cols)
+        oc = (C.c_int32 * len(ops))(*ops)
+        h = C.c_void_p()
+        check(lib().cylon_groupby(self._h, ic, C.c_int32(len(index)), ac, oc, C.c_int32(len(ops)), C.c_int32(1 if distributed else 0),
+                                  C.byref(h)))
+        return Table(h, self.ctx)

@@ -207,3 +207,105 @@ int cyl_gather_validity(const uint8_t *vsrc, const int64_t *idx, int64_t m, uint
 }
 
 }  // extern "C"
+
+// ---- concatenation / validity transport helpers (arrow::ConcatenateTables + CombineChunks, table.cpp:119-128,594-600) ----
+namespace cylb {
+
+__global__ void concat_offsets_kernel(const int32_t *__restrict__ a, int64_t na, const int32_t *__restrict__ b, int64_t nb,
+                                      int32_t *__restrict__ out) {
+  const int32_t a0 = na > 0 ? a[0] : 0;
+  const int32_t abytes = na > 0 ? a[na] - a0 : 0;
+  const int32_t b0 = nb > 0 ? b[0] : 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i <= na + nb; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = i <= na ? (na > 0 ? a[i] - a0 : 0) : abytes + (b[i - na] - b0);
+}
+
+__global__ void concat_validity_kernel(const uint8_t *__restrict__ va, int64_t na, const uint8_t *__restrict__ vb, int64_t nb,
+                                       uint32_t *__restrict__ out) {
+  const int64_t n = na + nb, npad = (n + 31) & ~31ll;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npad; i += (int64_t)gridDim.x * blockDim.x) {
+    bool v = false;
+    if (i < na) v = va ? bit_is_set(va, i) : true;
+    else if (i < n) v = vb ? bit_is_set(vb, i - na) : true;
+    const unsigned bits = __ballot_sync(0xffffffffu, v);
+    if (lane_id() == 0) out[i >> 5] = bits;
+  }
+}
+
+__global__ void unpack_validity_kernel(const uint8_t *__restrict__ bitmap, int64_t n, uint8_t *__restrict__ bytes) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    bytes[i] = bitmap ? (bit_is_set(bitmap, i) ? 1 : 0) : 1;
+}
+
+__global__ void pack_validity_kernel(const uint8_t *__restrict__ bytes, int64_t n, uint32_t *__restrict__ bitmap) {
+  const int64_t npad = (n + 31) & ~31ll;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npad; i += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned bits = __ballot_sync(0xffffffffu, i < n && bytes[i] != 0);
+    if (lane_id() == 0) bitmap[i >> 5] = bits;
+  }
+}
+
+__global__ void offsets_to_lengths_kernel(const int32_t *__restrict__ off, int64_t n, int32_t *__restrict__ len) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) len[i] = off[i + 1] - off[i];
+}
+
+__global__ void narrow_i64_i32_kernel(const int64_t *__restrict__ in, int64_t n1, int32_t *__restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n1; i += (int64_t)gridDim.x * blockDim.x) out[i] = (int32_t)in[i];
+}
+
+}  // namespace cylb
+
+extern "C" {
+
+int cyl_concat_offsets(const int32_t *a_offsets, int64_t na, const int32_t *b_offsets, int64_t nb, int32_t *out_offsets, void *stream) {
+  concat_offsets_kernel<<<grid1d(na + nb + 1), 256, 0, (cudaStream_t)stream>>>(a_offsets, na, b_offsets, nb, out_offsets);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_concat_validity(const uint8_t *va, int64_t na, const uint8_t *vb, int64_t nb, uint8_t *out, void *stream) {
+  if (na + nb <= 0) return CYL_OK;
+  concat_validity_kernel<<<grid1d(na + nb), 256, 0, (cudaStream_t)stream>>>(va, na, vb, nb, reinterpret_cast<uint32_t *>(out));
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_unpack_validity(const uint8_t *bitmap, int64_t n, uint8_t *bytes, void *stream) {
+  if (n <= 0) return CYL_OK;
+  unpack_validity_kernel<<<grid1d(n), 256, 0, (cudaStream_t)stream>>>(bitmap, n, bytes);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_pack_validity(const uint8_t *bytes, int64_t n, uint8_t *bitmap, void *stream) {
+  if (n <= 0) return CYL_OK;
+  pack_validity_kernel<<<grid1d(n), 256, 0, (cudaStream_t)stream>>>(bytes, n, reinterpret_cast<uint32_t *>(bitmap));
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_offsets_to_lengths(const int32_t *offsets, int64_t n, int32_t *lengths, void *stream) {
+  if (n <= 0) return CYL_OK;
+  offsets_to_lengths_kernel<<<grid1d(n), 256, 0, (cudaStream_t)stream>>>(offsets, n, lengths);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_lengths_to_offsets(const int32_t *lengths, int64_t n, int32_t *offsets, int64_t *total_bytes, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  Scratch o64;
+  CYL_TRY(o64.alloc((size_t)(n + 1) * sizeof(int64_t), s));
+  CYL_TRY(exclusive_scan<int32_t>(lengths, n, o64.as<int64_t>(), s));
+  narrow_i64_i32_kernel<<<grid1d(n + 1), 256, 0, s>>>(o64.as<int64_t>(), n + 1, offsets);
+  CYL_LAUNCH_CHECK();
+  if (total_bytes) {
+    int64_t t = 0;
+    CYL_CUDA(cudaMemcpyAsync(&t, o64.as<int64_t>() + n, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    CYL_CUDA(cudaStreamSynchronize(s));
+    if (t > 0x7FFFFFFFll) return fail(CYL_CapacityError, "variable-width column needs %lld bytes (> 2^31-1, int32 offsets)", (long long)t);
+    *total_bytes = t;
+  }
+  return CYL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,209 @@
+// context.cpp -- cylon::CylonContext and the NCCL communicator.
+//
+// Replaces (reference, relative to cpp/src/cylon/): ctx/cylon_context.cpp:24-108 and the transport stack
+// net/mpi/mpi_communicator.cpp:40-70, net/mpi/mpi_channel.cpp:30-247, net/ops/all_to_all.cpp:26-178. The reference
+// moves every Arrow buffer with a header Isend, a payload Isend and a FIN message per peer, polled with MPI_Test
+// from a busy loop. Here one process drives one GPU and a table shuffle is a single ncclGroupStart ...
+// ncclSend/ncclRecv x (P-1) x buffers ... ncclGroupEnd enqueued on the context's stream; NVSwitch gives every pair
+// of GPUs the full 900 GB/s per direction so the flat all-to-all needs no topology staging.
+// libnccl is resolved with dlopen at first use so that the library also loads on hosts without NCCL/GPU
+// (the build container); inside a torch process this binds to the libnccl.so.2 torch already loaded.
+#include "cylon/ctx/cylon_context.hpp"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <mutex>
+
+#include "util.hpp"
+
+namespace cylon {
+
+namespace {
+
+struct NcclApi {
+  void *handle = nullptr;
+  decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+  decltype(&ncclCommInitRank) CommInitRank = nullptr;
+  decltype(&ncclCommDestroy) CommDestroy = nullptr;
+  decltype(&ncclGroupStart) GroupStart = nullptr;
+  decltype(&ncclGroupEnd) GroupEnd = nullptr;
+  decltype(&ncclSend) Send = nullptr;
+  decltype(&ncclRecv) Recv = nullptr;
+  decltype(&ncclAllGather) AllGather = nullptr;
+  decltype(&ncclGetErrorString) GetErrorString = nullptr;
+  std::string error;
+};
+
+NcclApi *LoadNccl() {
+  static NcclApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) {
+      api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (api.handle) break;
+    }
+    if (!api.handle) {
+      api.error = std::string("cannot load libnccl.so.2: ") + dlerror();
+      return;
+    }
+#define LOAD(field, sym)                                                   \
+  api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, sym)); \
+  if (!api.field) api.error = std::string("libnccl lacks symbol ") + sym;
+    LOAD(GetUniqueId, "ncclGetUniqueId")
+    LOAD(CommInitRank, "ncclCommInitRank")
+    LOAD(CommDestroy, "ncclCommDestroy")
+    LOAD(GroupStart, "ncclGroupStart")
+    LOAD(GroupEnd, "ncclGroupEnd")
+    LOAD(Send, "ncclSend")
+    LOAD(Recv, "ncclRecv")
+    LOAD(AllGather, "ncclAllGather")
+    LOAD(GetErrorString, "ncclGetErrorString")
+#undef LOAD
+  });
+  return &api;
+}
+
+#define NCCL_RETURN_IF_FAILED(api, expr)                                                                        \
+  do {                                                                                                          \
+    ncclResult_t _r = (expr);                                                                                   \
+    if (_r != ncclSuccess) return Status(Code::ExecutionError, std::string("NCCL error: ") + (api)->GetErrorString(_r) + " in " #expr); \
+  } while (0)
+
+class NcclCommunicator : public net::Communicator {
+ public:
+  NcclCommunicator(NcclApi *api, ncclComm_t comm, int rank, int world) : api_(api), comm_(comm), rank_(rank), world_(world) {}
+  ~NcclCommunicator() override { Finalize(); }
+  int GetRank() const override { return rank_; }
+  int GetWorldSize() const override { return world_; }
+  net::CommType GetCommType() const override { return net::CommType::NCCL; }
+
+  void Barrier() override {
+    int64_t v = rank_;
+    std::vector<int64_t> all((size_t)world_);
+    AllGather(&v, 1, all.data(), nullptr);
+  }
+
+  void Finalize() override {
+    if (comm_) {
+      api_->CommDestroy(comm_);
+      comm_ = nullptr;
+    }
+  }
+
+  Status AllGather(const int64_t *send, int n, int64_t *recv, void *stream) override {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    detail::DevBuf ds, dr;
+    RETURN_CYLON_STATUS_IF_FAILED(ds.alloc((size_t)n * 8, stream));
+    RETURN_CYLON_STATUS_IF_FAILED(dr.alloc((size_t)n * 8 * world_, stream));
+    CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(ds.p, send, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    NCCL_RETURN_IF_FAILED(api_, api_->AllGather(ds.p, dr.p, (size_t)n, ncclInt64, comm_, s));
+    CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(recv, dr.p, (size_t)n * 8 * world_, cudaMemcpyDeviceToHost, s));
+    CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
+    return Status::OK();
+  }
+
+  Status AllToAllV(const std::vector<Exchange> &ex, void *stream) override {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // own slice: plain device copy, enqueued first so it overlaps the NVLink traffic
+    for (const auto &e : ex) {
+      const int64_t b = e.send_bytes[rank_];
+      if (b > 0)
+        CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(static_cast<char *>(e.recv) + e.recv_off[rank_], static_cast<const char *>(e.send) + e.send_off[rank_],
+                                              (size_t)b, cudaMemcpyDeviceToDevice, s));
+    }
+    NCCL_RETURN_IF_FAILED(api_, api_->GroupStart());
+    for (const auto &e : ex) {
+      for (int p = 0; p < world_; p++) {
+        if (p == rank_) continue;
+        if (e.send_bytes[p] > 0)
+          NCCL_RETURN_IF_FAILED(api_, api_->Send(static_cast<const char *>(e.send) + e.send_off[p], (size_t)e.send_bytes[p], ncclChar, p, comm_, s));
+        if (e.recv_bytes[p] > 0)
+          NCCL_RETURN_IF_FAILED(api_, api_->Recv(static_cast<char *>(e.recv) + e.recv_off[p], (size_t)e.recv_bytes[p], ncclChar, p, comm_, s));
+      }
+    }
+    NCCL_RETURN_IF_FAILED(api_, api_->GroupEnd());
+    return Status::OK();
+  }
+
+ private:
+  NcclApi *api_;
+  ncclComm_t comm_;
+  int rank_, world_;
+};
+
+thread_local std::string g_ctx_error;
+
+}  // namespace
+
+Status net::NcclConfig::CreateUniqueId(NcclUniqueId *out) {
+  NcclApi *api = LoadNccl();
+  if (!api->error.empty()) return Status(Code::ExecutionError, api->error);
+  static_assert(sizeof(ncclUniqueId) == sizeof(NcclUniqueId), "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  NCCL_RETURN_IF_FAILED(api, api->GetUniqueId(&id));
+  memcpy(out->bytes, &id, sizeof(id));
+  return Status::OK();
+}
+
+const std::string &CylonContext::LastError() { return g_ctx_error; }
+
+std::shared_ptr<CylonContext> CylonContext::Init() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  return Init(dev);
+}
+
+std::shared_ptr<CylonContext> CylonContext::Init(int device) {
+  if (cyl_init(device) != CYL_OK) {
+    g_ctx_error = cyl_last_error();
+    return nullptr;
+  }
+  auto ctx = std::make_shared<CylonContext>(false);
+  ctx->device = device;
+  return ctx;
+}
+
+std::shared_ptr<CylonContext> CylonContext::InitDistributed(const std::shared_ptr<net::CommConfig> &config) {
+  if (!config || config->Type() != net::CommType::NCCL) {
+    g_ctx_error = "InitDistributed: only CommType::NCCL is implemented (pass a cylon::net::NcclConfig)";
+    return nullptr;
+  }
+  auto nc = std::static_pointer_cast<net::NcclConfig>(config);
+  if (cyl_init(nc->device) != CYL_OK) {
+    g_ctx_error = cyl_last_error();
+    return nullptr;
+  }
+  NcclApi *api = LoadNccl();
+  if (!api->error.empty()) {
+    g_ctx_error = api->error;
+    return nullptr;
+  }
+  ncclUniqueId id;
+  memcpy(&id, nc->id.bytes, sizeof(id));
+  ncclComm_t comm = nullptr;
+  ncclResult_t r = api->CommInitRank(&comm, nc->world_size, id, nc->rank);
+  if (r != ncclSuccess) {
+    g_ctx_error = std::string("ncclCommInitRank failed: ") + api->GetErrorString(r);
+    return nullptr;
+  }
+  auto ctx = std::make_shared<CylonContext>(true);
+  ctx->device = nc->device;
+  ctx->communicator = std::make_shared<NcclCommunicator>(api, comm, nc->rank, nc->world_size);
+  return ctx;
+}
+
+void CylonContext::Finalize() {
+  if (communicator) communicator->Finalize();
+}
+
+std::vector<int> CylonContext::GetNeighbours(bool include_self) {
+  std::vector<int> n;
+  const int w = GetWorldSize(), r = GetRank();
+  for (int i = 0; i < w; i++)
+    if (include_self || i != r) n.push_back(i);
+  return n;
+}
+
+}  // namespace cylon

@@ -1,0 +1,113 @@
+// groupby.cpp -- HashGroupBy / DistributedHashGroupBy on the device.
+//
+// Replaces (reference, relative to cpp/src/cylon/): groupby/hash_groupby.cpp:250-360 and groupby/groupby.cpp:24-91.
+// Same control flow: project (index ++ aggregate columns), pre-aggregate locally when world == 1 or every op is in
+// {SUM, MIN, MAX} (groupby.cpp:24-31,60-67), shuffle on the index columns, aggregate again -- which is also why the
+// output column of a distributed associative aggregation is named "sum_sum_x" (SURVEY.md G1); kept for parity.
+#include "cylon/groupby/groupby.hpp"
+
+#include <algorithm>
+
+#include "table_ops.hpp"
+
+namespace cylon {
+
+Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_t> &idx_cols,
+                   const std::vector<std::pair<int32_t, compute::AggregationOpId>> &aggregations, std::shared_ptr<Table> &output) {
+  if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  std::vector<int> keys(idx_cols.begin(), idx_cols.end());
+  RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*table, keys, "HashGroupBy"));
+  for (const auto &a : aggregations) {
+    if (a.first < 0 || a.first >= table->Columns()) return Status(Code::IndexError, "HashGroupBy: aggregate column out of range");
+    if (a.second != compute::SUM && a.second != compute::MIN && a.second != compute::MAX && a.second != compute::COUNT)
+      return Status(Code::NotImplemented, "HashGroupBy: only SUM/MIN/MAX/COUNT run on the GPU path");
+  }
+  auto ctx = table->GetContext();
+  void *stream = ctx->GetStream();
+  const int64_t n = table->Rows();
+
+  // make_groups (hash_groupby.cpp:92-126)
+  detail::DevBuf gid, first;
+  RETURN_CYLON_STATUS_IF_FAILED(gid.alloc((size_t)(n + 1) * 8, stream));
+  RETURN_CYLON_STATUS_IF_FAILED(first.alloc((size_t)n + 1, stream));
+  const auto kd = detail::Descs(*table, keys);
+  int64_t groups = 0;
+  CYL_RETURN_IF_FAILED(cyl_groupby_hash(kd.data(), (int32_t)kd.size(), n, gid.as<int64_t>(), first.as<uint8_t>(), &groups, stream));
+
+  // key columns = first row of every group (hash_groupby.cpp:281-286)
+  std::shared_ptr<Table> key_table, filtered;
+  RETURN_CYLON_STATUS_IF_FAILED(table->Project(idx_cols, key_table));
+  RETURN_CYLON_STATUS_IF_FAILED(detail::FilterTable(key_table, first.as<uint8_t>(), &filtered));
+  std::vector<std::shared_ptr<Column>> cols = filtered->GetColumns();
+
+  // aggregates (hash_groupby.cpp:288-306); output name = prefix + input name (:197-199)
+  for (const auto &a : aggregations) {
+    const auto &src = table->GetColumn(a.first);
+    const bool count = a.second == compute::COUNT;
+    const int32_t type = count ? (int32_t)CYL_INT64 : src->type();
+    const int32_t width = count ? 8 : src->byte_width();
+    std::shared_ptr<Column> col;
+    RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(std::string(compute::AggregationPrefix(a.second)) + src->name(), type, width, groups,
+                                                   groups * (int64_t)width, false, stream, &col));
+    int op = 0;
+    switch (a.second) {
+      case compute::SUM: op = CYL_AGG_SUM; break;
+      case compute::MIN: op = CYL_AGG_MIN; break;
+      case compute::MAX: op = CYL_AGG_MAX; break;
+      default: op = CYL_AGG_COUNT; break;
+    }
+    CYL_RETURN_IF_FAILED(cyl_aggregate(&src->desc(), gid.as<int64_t>(), groups, op, col->mutable_data(), stream));
+    cols.push_back(col);
+  }
+  output = std::make_shared<Table>(std::move(cols), ctx);
+  return Status::OK();
+}
+
+Status HashGroupBy(const std::shared_ptr<Table> &table, int32_t idx_col, const std::vector<int32_t> &aggregate_cols,
+                   const std::vector<compute::AggregationOpId> &aggregate_ops, std::shared_ptr<Table> &output) {
+  if (aggregate_cols.size() != aggregate_ops.size()) return Status(Code::Invalid, "aggregate_cols size != aggregate_ops size");
+  std::vector<std::pair<int32_t, compute::AggregationOpId>> aggs;
+  for (size_t i = 0; i < aggregate_cols.size(); i++) aggs.emplace_back(aggregate_cols[i], aggregate_ops[i]);
+  return HashGroupBy(table, std::vector<int32_t>{idx_col}, aggs, output);
+}
+
+static bool is_associative(const std::vector<compute::AggregationOpId> &ops) {  // groupby.cpp:24-31
+  return std::all_of(ops.begin(), ops.end(), [](compute::AggregationOpId op) { return op == compute::SUM || op == compute::MIN || op == compute::MAX; });
+}
+
+Status DistributedHashGroupBy(std::shared_ptr<Table> &table, const std::vector<int32_t> &index_cols, const std::vector<int32_t> &aggregate_cols,
+                              const std::vector<compute::AggregationOpId> &aggregate_ops, std::shared_ptr<Table> &output) {
+  if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  if (aggregate_cols.size() != aggregate_ops.size()) return Status(Code::Invalid, "aggregate_cols size != aggregate_ops size");  // groupby.cpp:38-40
+  std::vector<int32_t> project_cols(index_cols);
+  project_cols.insert(project_cols.end(), aggregate_cols.begin(), aggregate_cols.end());
+  std::shared_ptr<Table> projected;
+  RETURN_CYLON_STATUS_IF_FAILED(table->Project(project_cols, projected));  // groupby.cpp:43-46
+  std::vector<int32_t> idx_after(index_cols.size());
+  for (size_t i = 0; i < idx_after.size(); i++) idx_after[i] = (int32_t)i;
+  std::vector<std::pair<int32_t, compute::AggregationOpId>> aggs;
+  for (size_t i = 0; i < aggregate_cols.size(); i++) aggs.emplace_back((int32_t)(index_cols.size() + i), aggregate_ops[i]);
+
+  const int world = table->GetContext()->GetWorldSize();
+  std::shared_ptr<Table> local;
+  if (world == 1 || is_associative(aggregate_ops)) {  // groupby.cpp:60-64
+    RETURN_CYLON_STATUS_IF_FAILED(HashGroupBy(projected, idx_after, aggs, local));
+  } else {
+    local = projected;
+  }
+  if (world > 1) {  // groupby.cpp:69-77
+    std::shared_ptr<Table> shuffled;
+    std::vector<int> hc(idx_after.begin(), idx_after.end());
+    RETURN_CYLON_STATUS_IF_FAILED(Shuffle(local, hc, shuffled));
+    return HashGroupBy(shuffled, idx_after, aggs, output);
+  }
+  output = local;
+  return Status::OK();
+}
+
+Status DistributedHashGroupBy(std::shared_ptr<Table> &table, int32_t index_col, const std::vector<int32_t> &aggregate_cols,
+                              const std::vector<compute::AggregationOpId> &aggregate_ops, std::shared_ptr<Table> &output) {
+  return DistributedHashGroupBy(table, std::vector<int32_t>{index_col}, aggregate_cols, aggregate_ops, output);
+}
+
+}  // namespace cylon

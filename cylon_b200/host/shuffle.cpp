@@ -1,0 +1,404 @@
+// shuffle.cpp -- hash partition -> all-to-all -> contiguous table, and the Distributed* operators built on it.
+//
+// Replaces (reference, relative to cpp/src/cylon/): table.cpp:67-131 (all_to_all_arrow_tables), :133-179
+// (shuffle_table_by_hashing / shuffle_two_tables_by_hashing), :482-502 (DistributedJoin), :727-785 (distributed set
+// operations), :910-921 (Shuffle), :984-999 (DistributedUnique), partition/partition.cpp:66-217 (Split,
+// MapToHashPartitions, PartitionByHashing) and arrow/arrow_all_to_all.cpp:24-268 (per-buffer framing).
+//
+// What is different by design:
+//  * the table is scattered ONCE into a partition-ordered copy (partition p's rows are contiguous, in input order);
+//    that copy is the send buffer -- no per-partition arrow::Table objects, no builders;
+//  * one AllGather of the P x (rows, bytes per variable-width column, has-nulls per column) count vector replaces the
+//    per-buffer header/FIN handshake; every receive offset is known before any payload moves, so each peer's slice
+//    lands directly at its final position in the output columns -- the reference's ConcatenateTables + CombineChunks
+//    copy (table.cpp:119-128) does not exist;
+//  * all column buffers of the table travel in one grouped ncclSend/ncclRecv; sizes are 64-bit (the reference is
+//    limited to 2 GiB per buffer per peer by `int` lengths, net/TxRequest.hpp:25);
+//  * received chunks are ordered by source rank (the reference orders by arrival: non-deterministic).
+#include <cuda_runtime.h>
+
+#include "cylon/partition/partition.hpp"
+#include "cylon/table.hpp"
+#include "table_ops.hpp"
+
+namespace cylon {
+
+namespace {
+
+using detail::DevBuf;
+
+struct Partitioned {
+  std::vector<std::shared_ptr<Column>> cols;  // partition-ordered copy
+  std::vector<int64_t> row_off;               // [P+1]
+  std::vector<std::vector<int64_t>> byte_off; // per var-width column: [P+1] byte offsets at partition boundaries (else empty)
+};
+
+// MapToHashPartitions + Split fused: returns the partition-ordered table and the partition boundaries (host)
+Status PartitionTable(const std::shared_ptr<Table> &table, const std::vector<int> &hash_cols, uint32_t P, Partitioned *out) {
+  auto ctx = table->GetContext();
+  void *stream = ctx->GetStream();
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t n = table->Rows();
+  const int ncols = table->Columns();
+  RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*table, hash_cols, "partition"));
+
+  bool simple = true;  // all fixed width of a vector-friendly size, no validity: one fused kernel pass
+  for (const auto &c : table->GetColumns()) {
+    const int w = c->byte_width();
+    if (c->is_var_width() || c->has_validity() || !(w == 1 || w == 2 || w == 4 || w == 8 || w == 16)) simple = false;
+  }
+  DevBuf part_offsets;
+  RETURN_CYLON_STATUS_IF_FAILED(part_offsets.alloc((P + 1) * sizeof(int64_t), stream));
+  out->cols.clear();
+  out->byte_off.assign((size_t)ncols, {});
+  for (const auto &c : table->GetColumns()) {
+    std::shared_ptr<Column> d;
+    RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(c->name(), c->type(), c->byte_width(), n, c->data_bytes(), c->has_validity(), stream, &d));
+    out->cols.push_back(d);
+  }
+  const auto all = detail::AllDescs(*table);
+  if (simple) {
+    std::vector<void *> dst;
+    for (auto &c : out->cols) dst.push_back(c->mutable_data());
+    std::vector<int32_t> keys(hash_cols.begin(), hash_cols.end());
+    CYL_RETURN_IF_FAILED(cyl_partition_scatter_fixed(all.data(), ncols, keys.data(), (int32_t)keys.size(), n, P, dst.data(),
+                                                     part_offsets.as<int64_t>(), stream));
+  } else {
+    DevBuf dest;
+    RETURN_CYLON_STATUS_IF_FAILED(dest.alloc((size_t)(n + 1) * 8, stream));
+    const auto kd = detail::Descs(*table, hash_cols);
+    CYL_RETURN_IF_FAILED(cyl_partition_map(kd.data(), (int32_t)kd.size(), n, P, nullptr, dest.as<int64_t>(), part_offsets.as<int64_t>(), stream));
+    for (int c = 0; c < ncols; c++) {
+      const cyl_column_t &src = all[c];
+      auto &d = out->cols[c];
+      if (d->is_var_width()) {
+        CYL_RETURN_IF_FAILED(cyl_scatter_varwidth(src.offsets, static_cast<const uint8_t *>(src.data), dest.as<int64_t>(), n,
+                                                  d->mutable_offsets(), static_cast<uint8_t *>(d->mutable_data()), stream));
+      } else {
+        CYL_RETURN_IF_FAILED(cyl_scatter_fixed(src.data, src.byte_width, dest.as<int64_t>(), n, d->mutable_data(), stream));
+      }
+      if (src.validity) CYL_RETURN_IF_FAILED(cyl_scatter_validity(src.validity, dest.as<int64_t>(), n, d->mutable_validity(), stream));
+    }
+  }
+  out->row_off.assign(P + 1, 0);
+  CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(out->row_off.data(), part_offsets.p, (P + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
+  // byte offsets of variable-width columns at the partition boundaries
+  std::vector<int32_t> tmp(P + 1, 0);
+  for (int c = 0; c < ncols; c++) {
+    if (!out->cols[c]->is_var_width()) continue;
+    for (uint32_t p = 0; p <= P; p++)
+      CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(&tmp[p], out->cols[c]->desc().offsets + out->row_off[p], 4, cudaMemcpyDeviceToHost, s));
+    CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
+    out->byte_off[c].assign(tmp.begin(), tmp.end());
+  }
+  return Status::OK();
+}
+
+// zero-copy slice of rows [r0, r1) of a partition-ordered table (fixed width, byte-aligned validity only when r0 % 8 == 0)
+Status SliceRows(const Partitioned &pt, const std::shared_ptr<CylonContext> &ctx, uint32_t p, std::shared_ptr<Table> *out) {
+  void *stream = ctx->GetStream();
+  const int64_t r0 = pt.row_off[p], r1 = pt.row_off[p + 1], m = r1 - r0;
+  std::vector<std::shared_ptr<Column>> cols;
+  for (size_t c = 0; c < pt.cols.size(); c++) {
+    const auto &src = pt.cols[c];
+    const cyl_column_t &d = src->desc();
+    std::shared_ptr<Column> col;
+    if (src->is_var_width()) {
+      const int64_t b0 = pt.byte_off[c][p], b1 = pt.byte_off[c][p + 1];
+      RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(src->name(), d.type, 0, m, b1 - b0, d.validity != nullptr, stream, &col));
+      CYL_RETURN_IF_FAILED(cyl_concat_offsets(d.offsets + r0, m, nullptr, 0, col->mutable_offsets(), stream));
+      CYL_RETURN_IF_FAILED(cyl_memcpy_d2d(col->mutable_data(), static_cast<const char *>(d.data) + b0, b1 - b0, stream));
+    } else {
+      const int64_t w = d.byte_width;
+      RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(src->name(), d.type, (int32_t)w, m, m * w, d.validity != nullptr, stream, &col));
+      CYL_RETURN_IF_FAILED(cyl_memcpy_d2d(col->mutable_data(), static_cast<const char *>(d.data) + r0 * w, m * w, stream));
+    }
+    if (d.validity) {
+      // re-align the bit range [r0, r1) to bit 0 through the byte form
+      DevBuf bytes;
+      RETURN_CYLON_STATUS_IF_FAILED(bytes.alloc((size_t)src->length() + 1, stream));
+      CYL_RETURN_IF_FAILED(cyl_unpack_validity(d.validity, src->length(), bytes.as<uint8_t>(), stream));
+      CYL_RETURN_IF_FAILED(cyl_pack_validity(bytes.as<uint8_t>() + r0, m, col->mutable_validity(), stream));
+    }
+    cols.push_back(col);
+  }
+  *out = std::make_shared<Table>(std::move(cols), ctx);
+  return Status::OK();
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------- partition API
+Status MapToHashPartitions(const std::shared_ptr<Table> &table, const std::vector<int32_t> &hash_column_idx, uint32_t num_partitions,
+                           uint32_t **target_partitions, uint64_t **partition_hist) {
+  std::vector<int> cols(hash_column_idx.begin(), hash_column_idx.end());
+  RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*table, cols, "MapToHashPartitions"));
+  void *stream = table->GetContext()->GetStream();
+  void *pid = nullptr, *hist = nullptr;
+  CYL_RETURN_IF_FAILED(cyl_malloc(&pid, (table->Rows() + 1) * 4));
+  CYL_RETURN_IF_FAILED(cyl_malloc(&hist, num_partitions * 8));
+  const auto kd = detail::Descs(*table, cols);
+  int rc = cyl_hash_partition(kd.data(), (int32_t)kd.size(), table->Rows(), num_partitions, static_cast<uint32_t *>(pid),
+                              static_cast<uint64_t *>(hist), stream);
+  if (rc != CYL_OK) {
+    cyl_free(pid);
+    cyl_free(hist);
+    return detail::FromCode(rc);
+  }
+  *target_partitions = static_cast<uint32_t *>(pid);
+  *partition_hist = static_cast<uint64_t *>(hist);
+  return Status::OK();
+}
+
+Status MapToHashPartitions(const std::shared_ptr<Table> &table, int32_t hash_column_idx, uint32_t num_partitions, uint32_t **target_partitions,
+                           uint64_t **partition_hist) {
+  return MapToHashPartitions(table, std::vector<int32_t>{hash_column_idx}, num_partitions, target_partitions, partition_hist);
+}
+
+Status Split(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *target_partitions, std::vector<std::shared_ptr<Table>> &output) {
+  auto ctx = table->GetContext();
+  void *stream = ctx->GetStream();
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int64_t n = table->Rows();
+  DevBuf dest, part_offsets;
+  RETURN_CYLON_STATUS_IF_FAILED(dest.alloc((size_t)(n + 1) * 8, stream));
+  RETURN_CYLON_STATUS_IF_FAILED(part_offsets.alloc((P + 1) * 8, stream));
+  CYL_RETURN_IF_FAILED(cyl_scatter_map(target_partitions, n, P, dest.as<int64_t>(), part_offsets.as<int64_t>(), stream));
+  Partitioned pt;
+  pt.byte_off.assign((size_t)table->Columns(), {});
+  for (const auto &c : table->GetColumns()) {
+    const cyl_column_t &src = c->desc();
+    std::shared_ptr<Column> d;
+    RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(c->name(), c->type(), c->byte_width(), n, c->data_bytes(), c->has_validity(), stream, &d));
+    if (c->is_var_width()) {
+      CYL_RETURN_IF_FAILED(cyl_scatter_varwidth(src.offsets, static_cast<const uint8_t *>(src.data), dest.as<int64_t>(), n, d->mutable_offsets(),
+                                                static_cast<uint8_t *>(d->mutable_data()), stream));
+    } else {
+      CYL_RETURN_IF_FAILED(cyl_scatter_fixed(src.data, src.byte_width, dest.as<int64_t>(), n, d->mutable_data(), stream));
+    }
+    if (src.validity) CYL_RETURN_IF_FAILED(cyl_scatter_validity(src.validity, dest.as<int64_t>(), n, d->mutable_validity(), stream));
+    pt.cols.push_back(d);
+  }
+  pt.row_off.assign(P + 1, 0);
+  CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(pt.row_off.data(), part_offsets.p, (P + 1) * 8, cudaMemcpyDeviceToHost, s));
+  CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
+  std::vector<int32_t> tmp(P + 1, 0);
+  for (size_t c = 0; c < pt.cols.size(); c++) {
+    if (!pt.cols[c]->is_var_width()) continue;
+    for (uint32_t p = 0; p <= P; p++)
+      CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(&tmp[p], pt.cols[c]->desc().offsets + pt.row_off[p], 4, cudaMemcpyDeviceToHost, s));
+    CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
+    pt.byte_off[c].assign(tmp.begin(), tmp.end());
+  }
+  output.clear();
+  for (uint32_t p = 0; p < P; p++) {
+    std::shared_ptr<Table> t;
+    RETURN_CYLON_STATUS_IF_FAILED(SliceRows(pt, ctx, p, &t));
+    output.push_back(t);
+  }
+  return Status::OK();
+}
+
+Status HashPartition(std::shared_ptr<Table> &table, const std::vector<int> &hash_columns, int no_of_partitions,
+                     std::unordered_map<int, std::shared_ptr<Table>> *out) {  // table.cpp:384-426
+  if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  if (no_of_partitions < 1) return Status(Code::Invalid, "no_of_partitions must be positive");
+  Partitioned pt;
+  RETURN_CYLON_STATUS_IF_FAILED(PartitionTable(table, hash_columns, (uint32_t)no_of_partitions, &pt));
+  for (int p = 0; p < no_of_partitions; p++) {
+    std::shared_ptr<Table> t;
+    RETURN_CYLON_STATUS_IF_FAILED(SliceRows(pt, table->GetContext(), (uint32_t)p, &t));
+    out->insert({p, t});
+  }
+  return Status::OK();
+}
+
+// ---------------------------------------------------------------------------------------------- shuffle
+static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &table, const std::vector<int> &hash_cols,
+                               std::shared_ptr<Table> &out) {
+  auto comm = ctx->GetCommunicator();
+  const int P = ctx->GetWorldSize(), rank = ctx->GetRank();
+  void *stream = ctx->GetStream();
+  const int ncols = table->Columns();
+
+  Partitioned pt;
+  RETURN_CYLON_STATUS_IF_FAILED(PartitionTable(table, hash_cols, (uint32_t)P, &pt));
+  std::vector<std::string> names = table->ColumnNames();
+  std::vector<int> has_validity(ncols);
+  for (int c = 0; c < ncols; c++) has_validity[c] = table->GetColumn(c)->has_validity() ? 1 : 0;
+  if (!table->IsRetain()) table.reset();  // table.cpp:152-154
+
+  // ---- count exchange: [rows to p]*P, then per var-width column [bytes to p]*P, then has-nulls per column
+  std::vector<int> var_cols;
+  for (int c = 0; c < ncols; c++)
+    if (pt.cols[c]->is_var_width()) var_cols.push_back(c);
+  const int nvec = P * (1 + (int)var_cols.size()) + ncols;
+  std::vector<int64_t> mine((size_t)nvec), all((size_t)nvec * P);
+  for (int p = 0; p < P; p++) mine[p] = pt.row_off[p + 1] - pt.row_off[p];
+  for (size_t v = 0; v < var_cols.size(); v++)
+    for (int p = 0; p < P; p++) mine[P * (1 + v) + p] = pt.byte_off[var_cols[v]][p + 1] - pt.byte_off[var_cols[v]][p];
+  for (int c = 0; c < ncols; c++) mine[P * (1 + var_cols.size()) + c] = has_validity[c];
+  RETURN_CYLON_STATUS_IF_FAILED(comm->AllGather(mine.data(), nvec, all.data(), stream));
+  auto at = [&](int src, int field) { return all[(size_t)src * nvec + field]; };
+
+  // ---- receive layout: chunks ordered by source rank
+  std::vector<int64_t> recv_rows(P), recv_row_off(P + 1, 0);
+  for (int sr = 0; sr < P; sr++) {
+    recv_rows[sr] = at(sr, rank);
+    recv_row_off[sr + 1] = recv_row_off[sr] + recv_rows[sr];
+  }
+  const int64_t total_rows = recv_row_off[P];
+  if (total_rows > 0xFFFFFFFEll) return Status(Code::CapacityError, "shuffle would put more than 2^32-2 rows on one GPU");
+
+  std::vector<std::shared_ptr<Column>> out_cols((size_t)ncols);
+  std::vector<net::Communicator::Exchange> ex;
+  std::vector<std::unique_ptr<DevBuf>> keep;  // staging that must outlive the exchange
+  struct Post { int col; DevBuf *lens; DevBuf *vbytes; };
+  std::vector<Post> posts;
+
+  auto add_exchange = [&](const void *send, void *recv, const std::vector<int64_t> &soff, const std::vector<int64_t> &sbytes,
+                          const std::vector<int64_t> &roff, const std::vector<int64_t> &rbytes) {
+    net::Communicator::Exchange e;
+    e.send = send;
+    e.recv = recv;
+    e.send_off = soff;
+    e.send_bytes = sbytes;
+    e.recv_off = roff;
+    e.recv_bytes = rbytes;
+    ex.push_back(std::move(e));
+  };
+  auto scaled = [&](const std::vector<int64_t> &v, int64_t w, size_t n) {
+    std::vector<int64_t> o(n);
+    for (size_t i = 0; i < n; i++) o[i] = v[i] * w;
+    return o;
+  };
+  std::vector<int64_t> send_rows(P), send_row_off(pt.row_off.begin(), pt.row_off.begin() + P);
+  for (int p = 0; p < P; p++) send_rows[p] = pt.row_off[p + 1] - pt.row_off[p];
+  std::vector<int64_t> recv_row_off_p(recv_row_off.begin(), recv_row_off.begin() + P);
+
+  int vidx = 0;
+  for (int c = 0; c < ncols; c++) {
+    const auto &src = pt.cols[c];
+    bool any_validity = false;
+    for (int sr = 0; sr < P; sr++) any_validity |= at(sr, P * (1 + (int)var_cols.size()) + c) != 0;
+    Post post{c, nullptr, nullptr};
+    if (src->is_var_width()) {
+      std::vector<int64_t> sbytes(P), soff(P), rbytes(P), roff(P + 1, 0);
+      for (int p = 0; p < P; p++) {
+        sbytes[p] = mine[P * (1 + vidx) + p];
+        soff[p] = pt.byte_off[c][p];
+        rbytes[p] = at(p, P * (1 + vidx) + rank);
+        roff[p + 1] = roff[p] + rbytes[p];
+      }
+      if (roff[P] > 0x7FFFFFFFll) return Status(Code::CapacityError, "shuffled variable-width column exceeds 2^31-1 bytes on one GPU");
+      RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(names[c], src->type(), 0, total_rows, roff[P], any_validity, stream, &out_cols[c]));
+      // lengths travel as int32 per row; offsets are rebuilt on the receiver
+      keep.emplace_back(new DevBuf());
+      DevBuf *slens = keep.back().get();
+      keep.emplace_back(new DevBuf());
+      DevBuf *rlens = keep.back().get();
+      RETURN_CYLON_STATUS_IF_FAILED(slens->alloc((size_t)(src->length() + 1) * 4, stream));
+      RETURN_CYLON_STATUS_IF_FAILED(rlens->alloc((size_t)(total_rows + 1) * 4, stream));
+      CYL_RETURN_IF_FAILED(cyl_offsets_to_lengths(src->desc().offsets, src->length(), slens->as<int32_t>(), stream));
+      add_exchange(slens->p, rlens->p, scaled(send_row_off, 4, P), scaled(send_rows, 4, P), scaled(recv_row_off_p, 4, P), scaled(recv_rows, 4, P));
+      std::vector<int64_t> roff_p(roff.begin(), roff.begin() + P);
+      add_exchange(src->desc().data, out_cols[c]->mutable_data(), soff, sbytes, roff_p, rbytes);
+      post.lens = rlens;
+      vidx++;
+    } else {
+      const int64_t w = src->byte_width();
+      RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(names[c], src->type(), (int32_t)w, total_rows, total_rows * w, any_validity, stream, &out_cols[c]));
+      add_exchange(src->desc().data, out_cols[c]->mutable_data(), scaled(send_row_off, w, P), scaled(send_rows, w, P), scaled(recv_row_off_p, w, P),
+                   scaled(recv_rows, w, P));
+    }
+    if (any_validity) {
+      keep.emplace_back(new DevBuf());
+      DevBuf *sv = keep.back().get();
+      keep.emplace_back(new DevBuf());
+      DevBuf *rv = keep.back().get();
+      RETURN_CYLON_STATUS_IF_FAILED(sv->alloc((size_t)src->length() + 1, stream));
+      RETURN_CYLON_STATUS_IF_FAILED(rv->alloc((size_t)total_rows + 1, stream));
+      CYL_RETURN_IF_FAILED(cyl_unpack_validity(src->desc().validity, src->length(), sv->as<uint8_t>(), stream));  // null bitmap -> all ones
+      add_exchange(sv->p, rv->p, send_row_off, send_rows, recv_row_off_p, recv_rows);
+      post.vbytes = rv;
+    }
+    posts.push_back(post);
+  }
+
+  RETURN_CYLON_STATUS_IF_FAILED(comm->AllToAllV(ex, stream));
+
+  for (const auto &post : posts) {
+    if (post.lens)
+      CYL_RETURN_IF_FAILED(cyl_lengths_to_offsets(post.lens->as<int32_t>(), total_rows, out_cols[post.col]->mutable_offsets(), nullptr, stream));
+    if (post.vbytes) CYL_RETURN_IF_FAILED(cyl_pack_validity(post.vbytes->as<uint8_t>(), total_rows, out_cols[post.col]->mutable_validity(), stream));
+  }
+  out = std::make_shared<Table>(std::move(out_cols), ctx);
+  return Status::OK();
+}
+
+Status Shuffle(std::shared_ptr<Table> &table, const std::vector<int> &hash_columns, std::shared_ptr<Table> &output) {  // table.cpp:910-921
+  if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  auto ctx = table->GetContext();
+  RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*table, hash_columns, "Shuffle"));
+  if (ctx->GetWorldSize() == 1) {  // one partition routed to ourselves: nothing to move
+    output = table;
+    return Status::OK();
+  }
+  return ShuffleByHashing(ctx, table, hash_columns, output);
+}
+
+static Status ShuffleTwo(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &left, const std::vector<int> &lcols,
+                         std::shared_ptr<Table> &right, const std::vector<int> &rcols, std::shared_ptr<Table> &lout, std::shared_ptr<Table> &rout) {
+  RETURN_CYLON_STATUS_IF_FAILED(ShuffleByHashing(ctx, left, lcols, lout));  // table.cpp:167-173
+  return ShuffleByHashing(ctx, right, rcols, rout);
+}
+
+Status DistributedJoin(std::shared_ptr<Table> &left, std::shared_ptr<Table> &right, const join::config::JoinConfig &cfg,
+                       std::shared_ptr<Table> &out) {
+  if (left == nullptr) return Status(Code::KeyError, "Couldn't find the left table");
+  if (right == nullptr) return Status(Code::KeyError, "Couldn't find the right table");
+  auto ctx = left->GetContext();
+  if (ctx->GetWorldSize() == 1) return Join(left, right, cfg, out);  // table.cpp:487
+  RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*left, cfg.GetLeftColumnIdx(), "DistributedJoin(left)"));
+  RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*right, cfg.GetRightColumnIdx(), "DistributedJoin(right)"));
+  std::shared_ptr<Table> l, r;
+  RETURN_CYLON_STATUS_IF_FAILED(ShuffleTwo(ctx, left, cfg.GetLeftColumnIdx(), right, cfg.GetRightColumnIdx(), l, r));
+  return Join(l, r, cfg, out);
+}
+
+typedef Status (*LocalSetOperation)(std::shared_ptr<Table> &, std::shared_ptr<Table> &, std::shared_ptr<Table> &);
+
+static Status DoDistributedSetOperation(LocalSetOperation op, std::shared_ptr<Table> &left, std::shared_ptr<Table> &right,
+                                        std::shared_ptr<Table> &out) {  // table.cpp:727-767
+  if (left == nullptr || right == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  RETURN_CYLON_STATUS_IF_FAILED(detail::VerifyTableSchema(*left, *right));
+  auto ctx = left->GetContext();
+  if (ctx->GetWorldSize() < 2) return op(left, right, out);
+  std::vector<int> all_cols;
+  for (int c = 0; c < left->Columns(); c++) all_cols.push_back(c);
+  std::shared_ptr<Table> l, r;
+  RETURN_CYLON_STATUS_IF_FAILED(ShuffleTwo(ctx, left, all_cols, right, all_cols, l, r));
+  return op(l, r, out);
+}
+
+Status DistributedUnion(std::shared_ptr<Table> &l, std::shared_ptr<Table> &r, std::shared_ptr<Table> &out) {
+  return DoDistributedSetOperation(&Union, l, r, out);
+}
+Status DistributedSubtract(std::shared_ptr<Table> &l, std::shared_ptr<Table> &r, std::shared_ptr<Table> &out) {
+  return DoDistributedSetOperation(&Subtract, l, r, out);
+}
+Status DistributedIntersect(std::shared_ptr<Table> &l, std::shared_ptr<Table> &r, std::shared_ptr<Table> &out) {
+  return DoDistributedSetOperation(&Intersect, l, r, out);
+}
+
+Status DistributedUnique(std::shared_ptr<Table> &in, const std::vector<int> &cols, std::shared_ptr<Table> &out) {  // table.cpp:984-999
+  if (in == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  auto ctx = in->GetContext();
+  if (ctx->GetWorldSize() == 1) return Unique(in, cols, out);
+  std::shared_ptr<Table> shuffled;
+  RETURN_CYLON_STATUS_IF_FAILED(Shuffle(in, cols, shuffled));
+  return Unique(shuffled, cols, out);
+}
+
+}  // namespace cylon

@@ -1,0 +1,65 @@
+// cylon::net::CommType / CommConfig / Communicator -- the transport seam of the reference
+// (cpp/src/cylon/net/comm_type.hpp:20-22, comm_config.hpp:22-36, communicator.hpp:24-37, channel.hpp:51-90),
+// with one added backend: NCCL over NVLink (one process per GPU). The reference's only backend is MPI
+// point-to-point with a header/payload/FIN handshake per buffer (net/mpi/mpi_channel.cpp); here a table shuffle is
+// one count exchange plus ONE grouped ncclSend/ncclRecv over all column buffers (cylon_b200/host/shuffle.cpp).
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../status.hpp"
+
+namespace cylon {
+namespace net {
+
+enum CommType { LOCAL = 0, MPI, TCP, UCX, NCCL };
+
+class CommConfig {
+ public:
+  virtual ~CommConfig() = default;
+  virtual CommType Type() = 0;
+};
+
+// 128-byte NCCL bootstrap id: rank 0 creates it (NcclConfig::CreateUniqueId) and hands it to the other ranks by any
+// out-of-band channel (torch.distributed broadcast, a file, MPI_Bcast ...).
+struct NcclUniqueId {
+  char bytes[128];
+};
+
+class NcclConfig : public CommConfig {
+ public:
+  NcclConfig(int rank, int world_size, int device, const NcclUniqueId &id) : rank(rank), world_size(world_size), device(device), id(id) {}
+  static std::shared_ptr<NcclConfig> Make(int rank, int world_size, int device, const NcclUniqueId &id) {
+    return std::make_shared<NcclConfig>(rank, world_size, device, id);
+  }
+  static Status CreateUniqueId(NcclUniqueId *out);
+  CommType Type() override { return CommType::NCCL; }
+  int rank, world_size, device;
+  NcclUniqueId id;
+};
+
+// What the shuffle needs from a transport. All buffers are device memory; counts and offsets are in bytes.
+class Communicator {
+ public:
+  virtual ~Communicator() = default;
+  virtual int GetRank() const = 0;
+  virtual int GetWorldSize() const = 0;
+  virtual CommType GetCommType() const = 0;
+  virtual void Barrier() = 0;
+  virtual void Finalize() = 0;
+  // every rank contributes n int64 values (host memory); recv gets world*n values ordered by rank
+  virtual Status AllGather(const int64_t *send, int n, int64_t *recv, void *stream) = 0;
+  struct Exchange {  // one buffer class of one column
+    const void *send = nullptr;
+    void *recv = nullptr;
+    std::vector<int64_t> send_off, send_bytes, recv_off, recv_bytes;  // per peer
+  };
+  // one grouped all-to-all over every exchange; the own-rank slice is a device-to-device copy
+  virtual Status AllToAllV(const std::vector<Exchange> &exchanges, void *stream) = 0;
+};
+
+}  // namespace net
+}  // namespace cylon

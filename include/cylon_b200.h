@@ -152,6 +152,22 @@ int cyl_rowset_mask(const cyl_column_t *lcols /* host array */, const cyl_column
  * idx must hold n entries; *count is a host out (synchronises). Replaces arrow::compute::Filter's selection. */
 int cyl_mask_to_indices(const uint8_t *mask, int64_t n, int64_t *idx, int64_t *count /* host out */, void *stream);
 
+/* ---------------------------------------------------------------- concatenation / transport ---- */
+/* Pieces of arrow::ConcatenateTables + CombineChunks (table.cpp:119-128,594-600) for device columns; fixed-width
+ * data and variable-width bytes are plain device copies, these do the parts that are not. */
+/* out_offsets[0..na+nb] for the concatenation of two variable-width columns (each rebased to start at 0). */
+int cyl_concat_offsets(const int32_t *a_offsets, int64_t na, const int32_t *b_offsets, int64_t nb, int32_t *out_offsets, void *stream);
+/* bitmap of na+nb bits = va's bits then vb's bits; a NULL input means "all valid". ceil((na+nb)/32)*4 bytes. */
+int cyl_concat_validity(const uint8_t *va, int64_t na, const uint8_t *vb, int64_t nb, uint8_t *out, void *stream);
+/* validity bitmap <-> one byte per row (the shuffle moves validity as bytes because partition boundaries are not
+ * byte aligned in a bitmap; arrow_all_to_all.cpp:97-107 ships the raw bitmap of already-split arrays). */
+int cyl_unpack_validity(const uint8_t *bitmap /* NULL = all valid */, int64_t n, uint8_t *bytes, void *stream);
+int cyl_pack_validity(const uint8_t *bytes, int64_t n, uint8_t *bitmap, void *stream);
+/* int32 offsets <-> per-row lengths (the shuffle ships lengths and rebuilds offsets on the receiver).
+ * cyl_lengths_to_offsets: *total_bytes is a host out (may be NULL; when given the call synchronises). */
+int cyl_offsets_to_lengths(const int32_t *offsets, int64_t n, int32_t *lengths, void *stream);
+int cyl_lengths_to_offsets(const int32_t *lengths, int64_t n, int32_t *offsets, int64_t *total_bytes /* host out */, void *stream);
+
 /* ---------------------------------------------------------------- checks ----------------------- */
 /* Order-independent checksum of a table: sum over rows of a 64-bit mix of the row's values (nulls count as
  * zero bits + validity 0). No counterpart in the reference; it is how full-size results are compared with the

@@ -62,3 +62,38 @@ def assert_same_rows(got, expected, what=""):
     assert len(g) == len(e), "%s: %d rows, expected %d" % (what, len(g), len(e))
     for a, b in zip(g, e):
         assert a == b, "%s: row %r != expected %r" % (what, a, b)
+
+
+def to_orc(table):
+    """cylon_b200.api.Table -> oracle table (list of HCol), for multiset comparison."""
+    cols = []
+    for c in table.to_host():
+        validity = None
+        if c["valid"] is not None:
+            validity = np.packbits(c["valid"], bitorder="little")
+        if c["type"] in (orc.STRING, orc.BINARY):
+            cols.append(orc.HCol(c["type"], c["data"], c["offsets"], validity, name=c["name"]))
+        elif c["type"] == orc.FIXED_SIZE_BINARY:
+            cols.append(orc.HCol(c["type"], c["data"], None, validity, byte_width=c["byte_width"], name=c["name"]))
+        else:
+            cols.append(orc.HCol(c["type"], c["data"], None, validity, name=c["name"]))
+    return cols
+
+
+def from_orc(api, ctx, ocols):
+    """oracle table -> device table through the public API (host buffers in, H2D inside)."""
+    columns, types, validity, names = [], [], [], []
+    any_valid = False
+    for c in ocols:
+        if c.type in (orc.STRING, orc.BINARY):
+            columns.append((c.offsets, c.data))
+        else:
+            columns.append(c.data)
+        types.append(c.type)
+        names.append(c.name)
+        if c.validity is not None:
+            validity.append(c.valid_mask())
+            any_valid = True
+        else:
+            validity.append(None)
+    return api.Table.from_numpy(ctx, columns, names=names, types=types, validity=validity if any_valid else None)
