@@ -1,0 +1,115 @@
+"""ctypes binding of oracle/_ref/libcylon_ref.so: the reference's OWN code (hash partition kernels, hash join, sort
+join, build_final_table) compiled in place from /root/reference against pyarrow's Arrow C++. TEST INFRASTRUCTURE
+ONLY -- it pins the oracle (tests/test_oracle_vs_reference.py) and serves as the "reference" CPU baseline of bench.py.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import pyoracle as orc
+
+_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libcylon_ref.so")
+_lib = None
+
+
+def available():
+    return os.path.exists(_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(_PATH)
+        _lib.ref_table_rows.restype = C.c_int64
+        _lib.ref_table_col_bytes.restype = C.c_int64
+    return _lib
+
+
+class RefColIn(C.Structure):
+    _fields_ = [("type", C.c_int32), ("width", C.c_int32), ("n", C.c_int64), ("offsets", C.c_void_p), ("data", C.c_void_p)]
+
+
+def _args(col):
+    data = col.data if col.data.size else np.zeros(1, dtype=col.data.dtype)
+    offs = col.offsets.ctypes.data if col.offsets is not None else None
+    return (C.c_int32(col.type), C.c_int32(col.byte_width), C.c_int64(col.length), C.c_void_p(offs), C.c_void_p(data.ctypes.data)), data
+
+
+def row_hash(cols):
+    h = np.zeros(max(1, cols[0].length), dtype=np.uint32)
+    for c in cols:
+        a, _k = _args(c)
+        rc = lib().ref_update_hash(*a, h.ctypes.data_as(C.c_void_p))
+        assert rc == 0, rc
+    return h[: cols[0].length]
+
+
+def hash_partition(cols, num_partitions):
+    n = cols[0].length
+    pid = np.zeros(max(1, n), dtype=np.uint32)
+    hist = np.zeros(num_partitions, dtype=np.uint32)
+    for c in cols[:-1]:
+        a, _k = _args(c)
+        assert lib().ref_update_hash(*a, pid.ctypes.data_as(C.c_void_p)) == 0
+    a, _k = _args(cols[-1])
+    assert lib().ref_partition(*a, C.c_uint32(num_partitions), pid.ctypes.data_as(C.c_void_p), hist.ctypes.data_as(C.c_void_p)) == 0
+    return pid[:n], hist.astype(np.uint64)
+
+
+def array_index_hash_join(lkey, rkey, join_type):
+    la, _k1 = _args(lkey)
+    ra, _k2 = _args(rkey)
+    lp, rp, m = C.c_void_p(), C.c_void_p(), C.c_int64()
+    rc = lib().ref_array_index_hash_join(la[0], la[1], la[2], la[3], la[4], ra[2], ra[3], ra[4], C.c_int32(join_type), C.byref(lp),
+                                         C.byref(rp), C.byref(m))
+    assert rc == 0, rc
+    n = m.value
+    li = np.ctypeslib.as_array(C.cast(lp, C.POINTER(C.c_int64)), shape=(max(1, n),))[:n].copy()
+    ri = np.ctypeslib.as_array(C.cast(rp, C.POINTER(C.c_int64)), shape=(max(1, n),))[:n].copy()
+    lib().ref_free(lp)
+    lib().ref_free(rp)
+    return li, ri
+
+
+def _table_in(cols):
+    arr = (RefColIn * len(cols))()
+    keep = []
+    for i, c in enumerate(cols):
+        data = c.data if c.data.size else np.zeros(1, dtype=c.data.dtype)
+        keep.append(data)
+        arr[i].type, arr[i].width, arr[i].n = c.type, c.byte_width, c.length
+        arr[i].offsets = c.offsets.ctypes.data if c.offsets is not None else None
+        arr[i].data = data.ctypes.data
+    return arr, keep
+
+
+def join_tables(left, right, lkeys, rkeys, join_type, algorithm):
+    """cylon::join::JoinTables of the reference -> oracle-style table (list of HCol)."""
+    la, _k1 = _table_in(left)
+    ra, _k2 = _table_in(right)
+    lk = (C.c_int32 * len(lkeys))(*lkeys)
+    rk = (C.c_int32 * len(rkeys))(*rkeys)
+    h = C.c_void_p()
+    rc = lib().ref_join_tables(la, len(left), ra, len(right), lk, rk, len(lkeys), C.c_int32(join_type), C.c_int32(algorithm), C.byref(h))
+    assert rc == 0, rc
+    n = lib().ref_table_rows(h)
+    out = []
+    for c, src in enumerate(list(left) + list(right)):
+        nbytes = lib().ref_table_col_bytes(h, c)
+        valid = np.ones(max(1, n), dtype=np.uint8)
+        if src.type in (orc.STRING, orc.BINARY):
+            data = np.zeros(max(1, nbytes), dtype=np.uint8)
+            offs = np.zeros(n + 1, dtype=np.int32)
+            lib().ref_table_copy_col(h, c, C.c_void_p(data.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_void_p(valid.ctypes.data))
+            col = orc.HCol(src.type, data[:nbytes], offs)
+        else:
+            data = np.zeros(max(1, n), dtype=src.data.dtype)
+            lib().ref_table_copy_col(h, c, C.c_void_p(data.ctypes.data), None, C.c_void_p(valid.ctypes.data))
+            col = orc.HCol(src.type, data[:n])
+        v = valid[:n].astype(bool)
+        if not v.all():
+            col.validity = np.packbits(v, bitorder="little")
+        out.append(col)
+    lib().ref_table_free(h)
+    return out

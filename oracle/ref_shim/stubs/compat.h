@@ -1,0 +1,33 @@
+// Force-included (-include) when compiling the reference IN PLACE against Arrow 24 (the reference pins Arrow 2.0).
+// It restores two names Arrow 2 had and stands in for one reference header whose MemoryPool overrides no longer match
+// Arrow's virtual signatures (ctx/arrow_memory_pool_utils.hpp, skipped through its include guard). Checker build only;
+// the reference sources are not modified or copied.
+#pragma once
+#include <arrow/memory_pool.h>
+
+#include <memory>
+#include <string>
+#include <string_view>
+
+namespace arrow {
+namespace util {
+class string_view : public std::string_view {
+ public:
+  using std::string_view::string_view;
+  string_view(std::string_view v) : std::string_view(v) {}  // NOLINT implicit on purpose
+  std::string to_string() const { return std::string(*this); }
+};
+}  // namespace util
+}  // namespace arrow
+namespace std {
+template <>
+struct hash<arrow::util::string_view> {
+  size_t operator()(const arrow::util::string_view &v) const noexcept { return std::hash<std::string_view>()(v); }
+};
+}  // namespace std
+
+#define CYLON_SRC_CYLON_CTX_ARROW_MEMORY_POOL_UTILS_HPP_
+namespace cylon {
+class CylonContext;
+arrow::MemoryPool *ToArrowPool(const std::shared_ptr<cylon::CylonContext> &ctx);
+}  // namespace cylon
