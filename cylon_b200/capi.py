@@ -325,3 +325,50 @@ def mask_to_indices(mask, stream=None):
     cnt = C.c_int64()
     check(lib().cyl_mask_to_indices(_p(mb), C.c_int64(n), _p(idx), C.byref(cnt), C.c_void_p(stream)))
     return idx.to_numpy(np.int64, cnt.value)
+
+
+def pinned_array(shape, dtype):
+    """numpy array over cudaHostAlloc'ed (page-locked) memory; freed when the array is garbage collected."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) if not isinstance(shape, int) else int(shape)
+    nbytes = max(16, n * dtype.itemsize)
+    p = C.c_void_p()
+    check(lib().cyl_host_alloc_pinned(C.byref(p), C.c_int64(nbytes)))
+    buf = (C.c_uint8 * nbytes).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=n)
+    _PINNED[id(buf)] = (buf, p.value)
+    import weakref
+    weakref.finalize(arr, _free_pinned, id(buf))
+    return arr
+
+
+_PINNED = {}
+
+
+def _free_pinned(key):
+    ent = _PINNED.pop(key, None)
+    if ent is not None:
+        try:
+            lib().cyl_host_free_pinned(C.c_void_p(ent[1]))
+        except Exception:
+            pass
+
+
+def launch_count():
+    lib().cyl_launch_count.restype = C.c_longlong
+    return int(lib().cyl_launch_count())
+
+
+def profile_enable(on=True):
+    check(lib().cyl_profile_enable(C.c_int32(1 if on else 0)))
+
+
+def profile_report():
+    """-> {kernel: (launches, total_ms)}; synchronises the device and clears the records."""
+    buf = C.create_string_buffer(1 << 16)
+    check(lib().cyl_profile_report(buf, C.c_int64(len(buf))))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, n, ms = line.rsplit(",", 2)
+        out[name] = (int(n), float(ms))
+    return out

@@ -30,7 +30,22 @@ int cuda_fail(cudaError_t e, const char *expr, const char *file, int line);
     if (_rc != CYL_OK) return _rc; \
   } while (0)
 
-#define CYL_LAUNCH_CHECK() CYL_CUDA(cudaGetLastError())
+// every kernel launch is followed by this: counts the launch (cyl_launch_count) and surfaces launch errors
+void note_launch();
+#define CYL_LAUNCH_CHECK()        \
+  do {                            \
+    ::cylb::note_launch();        \
+    CYL_CUDA(cudaGetLastError()); \
+  } while (0)
+
+// Optional per-kernel timing with CUDA events on the launching stream (cyl_profile_enable). Off by default: the
+// scope object then costs one branch.
+struct ProfScope {
+  int slot = -1;
+  cudaStream_t s = nullptr;
+  ProfScope(const char *name, cudaStream_t stream);
+  ~ProfScope();
+};
 
 // Stream-ordered scratch buffer (cudaMallocAsync from the device's default pool; freed on the same stream).
 struct Scratch {

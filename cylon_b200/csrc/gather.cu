@@ -138,6 +138,7 @@ static inline int grid1d(int64_t n, int per_block = 256) {
 
 int gather_fixed(const void *src, int32_t w, const int64_t *idx, int64_t m, void *dst, uint8_t *validity, cudaStream_t s) {
   if (m == 0) return CYL_OK;
+  ProfScope ps("gather_fixed", s);
   uint32_t *v = reinterpret_cast<uint32_t *>(validity);
   const int g = grid1d(m, kGatherThreads * kGatherItems);
   switch (w) {

@@ -183,6 +183,7 @@ int hash_join_materialize(cyl_join_plan *p, int64_t *l_idx, int64_t *r_idx, cuda
   a.r_idx = r_idx;
   a.extra_base = p->m_probe;
   if (p->np > 0) {
+    ProfScope ps("hash_join_probe_write", s);
     hash_probe_write_kernel<<<grid1d(p->np), 256, 0, s>>>(a);
     CYL_LAUNCH_CHECK();
   }
@@ -265,17 +266,28 @@ int cyl_hash_join_count(const cyl_column_t *lkeys, const cyl_column_t *rkeys, in
   HashJoinArgs a;
   fill_args(p, &a);
   a.pcount = pcount.as<uint32_t>();
-  init_slots_kernel<<<grid1d(p->cap + 1), 256, 0, s>>>(table, p->cap + 1);
+  {
+    ProfScope ps("hash_join_init_slots", s);
+    init_slots_kernel<<<grid1d(p->cap + 1), 256, 0, s>>>(table, p->cap + 1);
+    note_launch();
+  }
   PLAN_CUDA(cudaGetLastError());
   if (p->nb > 0) {
+    ProfScope ps("hash_join_build", s);
     hash_build_kernel<<<grid1d(p->nb), 256, 0, s>>>(a);
+    note_launch();
     PLAN_CUDA(cudaGetLastError());
   }
   if (p->np > 0) {
+    ProfScope ps("hash_join_probe_count", s);
     hash_probe_count_kernel<<<grid1d(p->np), 256, 0, s>>>(a);
+    note_launch();
     PLAN_CUDA(cudaGetLastError());
   }
-  PLAN_TRY(exclusive_scan<uint32_t>(pcount.as<uint32_t>(), p->np, p->out_off, s));
+  {
+    ProfScope ps("hash_join_scan", s);
+    PLAN_TRY(exclusive_scan<uint32_t>(pcount.as<uint32_t>(), p->np, p->out_off, s));
+  }
   int64_t totals[2] = {0, 0};
   PLAN_CUDA(cudaMemcpyAsync(&totals[0], p->out_off + p->np, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
   if (join_type == CYL_JOIN_FULL_OUTER) {

@@ -220,8 +220,14 @@ static int partition_map_impl(const DCols *keys, const uint32_t *pid_in, int64_t
   CYL_TRY(hist.alloc((size_t)ncounters * sizeof(uint32_t), stream));
   CYL_TRY(base.alloc((size_t)(ncounters + 1) * sizeof(int64_t), stream));
   a.tile_hist = hist.as<uint32_t>();
-  CYL_TRY(launch_part<PM_TILE_HIST>(a, (size_t)kPartWarps * P * sizeof(uint32_t), stream));
-  CYL_TRY(exclusive_scan<uint32_t>(hist.as<uint32_t>(), ncounters, base.as<int64_t>(), stream));
+  {
+    ProfScope ps(digit_keys ? "radix_tile_hist" : "partition_tile_hist", stream);
+    CYL_TRY(launch_part<PM_TILE_HIST>(a, (size_t)kPartWarps * P * sizeof(uint32_t), stream));
+  }
+  {
+    ProfScope ps(digit_keys ? "radix_scan" : "partition_scan", stream);
+    CYL_TRY(exclusive_scan<uint32_t>(hist.as<uint32_t>(), ncounters, base.as<int64_t>(), stream));
+  }
   if (part_offsets) {
     extract_part_offsets<<<(P + 1 + 255) / 256, 256, 0, stream>>>(base.as<int64_t>(), a.ntiles, P, part_offsets);
     CYL_LAUNCH_CHECK();
@@ -229,7 +235,10 @@ static int partition_map_impl(const DCols *keys, const uint32_t *pid_in, int64_t
   a.tile_base = base.as<int64_t>();
   a.dest = dest;
   if (sc) a.sc = *sc;
-  CYL_TRY(launch_part<PM_DEST>(a, (size_t)kPartWarps * P * sizeof(int64_t), stream));
+  {
+    ProfScope ps(digit_keys ? "radix_scatter" : "partition_scatter", stream);
+    CYL_TRY(launch_part<PM_DEST>(a, (size_t)kPartWarps * P * sizeof(int64_t), stream));
+  }
   return CYL_OK;
 }
 

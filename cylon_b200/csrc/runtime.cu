@@ -2,7 +2,11 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
+#include <map>
 #include <mutex>
+#include <string>
+#include <vector>
 
 #include "common.cuh"
 
@@ -41,6 +45,35 @@ void Scratch::release() {
     cudaFreeAsync(p, s);
     p = nullptr;
   }
+}
+
+// ---- launch counter + event profiler ------------------------------------------------------------------------
+static std::atomic<long long> g_launches{0};
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+struct ProfRecord {
+  const char *name;
+  cudaEvent_t start, stop;
+};
+static std::atomic<int> g_prof_enabled{0};
+static std::mutex g_prof_mu;
+static std::vector<ProfRecord> g_prof_records;
+
+ProfScope::ProfScope(const char *name, cudaStream_t stream) : s(stream) {
+  if (!g_prof_enabled.load(std::memory_order_relaxed)) return;
+  ProfRecord r;
+  r.name = name;
+  if (cudaEventCreate(&r.start) != cudaSuccess || cudaEventCreate(&r.stop) != cudaSuccess) return;
+  cudaEventRecord(r.start, stream);
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_records.push_back(r);
+  slot = (int)g_prof_records.size() - 1;
+}
+
+ProfScope::~ProfScope() {
+  if (slot < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  cudaEventRecord(g_prof_records[slot].stop, s);
 }
 
 int num_sms() {
@@ -116,6 +149,43 @@ int cyl_init(int32_t device) {
   CYL_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
   uint64_t threshold = UINT64_MAX;  // keep freed scratch in the pool: no cudaMalloc/cudaFree on the hot path
   CYL_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+  return CYL_OK;
+}
+
+long long cyl_launch_count(void) { return g_launches.load(); }
+
+int cyl_profile_enable(int32_t on) {
+  g_prof_enabled.store(on ? 1 : 0);
+  return CYL_OK;
+}
+
+// Synchronises the device, folds the recorded scopes into "name,launches,total_ms\n" lines and clears them.
+int cyl_profile_report(char *buf, int64_t buf_len) {
+  CYL_CUDA(cudaDeviceSynchronize());
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  std::map<std::string, std::pair<long long, double>> agg;
+  for (auto &r : g_prof_records) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.start, r.stop) == cudaSuccess) {
+      auto &a = agg[r.name];
+      a.first += 1;
+      a.second += ms;
+    }
+    cudaEventDestroy(r.start);
+    cudaEventDestroy(r.stop);
+  }
+  g_prof_records.clear();
+  std::string out;
+  for (auto &kv : agg) {
+    char line[256];
+    snprintf(line, sizeof(line), "%s,%lld,%.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    out += line;
+  }
+  if (buf && buf_len > 0) {
+    const size_t n = out.size() < (size_t)buf_len - 1 ? out.size() : (size_t)buf_len - 1;
+    memcpy(buf, out.data(), n);
+    buf[n] = 0;
+  }
   return CYL_OK;
 }
 

@@ -39,6 +39,13 @@ int cyl_memcpy_d2d(void *dst, const void *src, int64_t bytes, void *stream);
 int cyl_stream_sync(void *stream);
 int cyl_host_alloc_pinned(void **ptr /* host out */, int64_t bytes);
 int cyl_host_free_pinned(void *ptr);
+/* Measurement hooks (no counterpart in the reference, which logs std::chrono stage times, e.g. hash_join.cpp:301-304).
+ * cyl_launch_count: kernels launched by this library since load. cyl_profile_enable(1) brackets the library's main
+ * kernels with CUDA events on their stream; cyl_profile_report synchronises the device and writes
+ * "kernel,launches,total_ms" lines (then clears the records). */
+long long cyl_launch_count(void);
+int cyl_profile_enable(int32_t on);
+int cyl_profile_report(char *buf /* host */, int64_t buf_len);
 
 /* ---------------------------------------------------------------- A: row hashing / partition --- */
 /* h[i] = chain over `cols` of 31*h + colhash(v), h0 = 0: ints/temporal (uint32_t)v, float/double/fixed
