@@ -12,6 +12,8 @@
 // pass 2 recomputes the partition ids (cheaper than storing 4 B/row) and either emits dest[] or scatters every
 // fixed-width column directly. The scattered stores of one warp form <= P short runs that the 126 MB L2 merges
 // into full lines before they reach HBM.
+#include <mutex>
+
 #include "common.cuh"
 #include "scan.cuh"
 
@@ -314,6 +316,37 @@ int scatter_fixed(const void *src, int32_t w, const int64_t *dest, int64_t n, vo
   return CYL_OK;
 }
 
+// ---- stable scatter map for callers that cannot allocate ---------------------------------------------------------
+// The three scratch arrays of the scatter map (per-tile histograms, their scanned cursors, the scan's tile sums) live
+// in ONE file-scope device array instead of coming from cudaMallocAsync. Its size bounds the problem:
+// tiles x partitions <= kStaticMaxCounters.
+constexpr int64_t kStaticMaxCounters = 262144;
+struct StaticScatterScratch {
+  int64_t base[kStaticMaxCounters + 1];                       // scanned cursors, [P][ntiles] (+ total)
+  int64_t scan_tiles[kStaticMaxCounters / kScanTile + 2];     // tile sums of the device scan
+  uint32_t hist[kStaticMaxCounters];                          // per-tile histograms, [P][ntiles]
+};
+static __device__ __align__(256) unsigned char g_static_scatter_scratch[sizeof(StaticScatterScratch)];
+
+// In host code the name above is only a handle: the address a kernel can use has to be asked for, once per device and
+// with that device current. Cached per device ordinal.
+static int static_scatter_scratch(StaticScatterScratch **out) {
+  static std::mutex mu;
+  static StaticScatterScratch *per_device[64] = {nullptr};
+  int dev = -1;
+  CYL_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(CYL_Invalid, "cyl_scatter_map_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (per_device[dev] == nullptr) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scatter_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_scatter_scratch)", __FILE__, __LINE__);
+    per_device[dev] = static_cast<StaticScatterScratch *>(p);
+  }
+  *out = per_device[dev];
+  return CYL_OK;
+}
+
 // one stable 8-bit LSD radix pass over (u64 key, u32 value) pairs; shares the warp-tile ranking above
 int radix_pass_pairs(const uint64_t *keys_in, const uint32_t *vals_in, uint64_t *keys_out, uint32_t *vals_out, int64_t n, int shift,
                      cudaStream_t stream) {
@@ -366,6 +399,45 @@ int cyl_hash_partition(const cyl_column_t *cols, int32_t ncols, int64_t nrows, u
 int cyl_scatter_map(const uint32_t *pid, int64_t nrows, uint32_t P, int64_t *dest, int64_t *part_offsets, void *stream) {
   if (nrows > 0 && (!pid || !dest)) return fail(CYL_Invalid, "cyl_scatter_map: null pid/dest");
   return partition_map_impl(nullptr, pid, nrows, P, nullptr, dest, nullptr, part_offsets, (cudaStream_t)stream, "cyl_scatter_map");
+}
+
+int cyl_scatter_map_static(const uint32_t *pid, int64_t nrows, uint32_t P, int64_t *dest, int64_t *part_offsets, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (P == 0 || P > 1024) return fail(CYL_Invalid, "cyl_scatter_map_static: num_partitions must be in [1, 1024], got %u", P);
+  if (nrows < 0) return fail(CYL_Invalid, "cyl_scatter_map_static: negative row count");
+  if (!part_offsets || (nrows > 0 && (!pid || !dest))) return fail(CYL_Invalid, "cyl_scatter_map_static: null pid/dest/part_offsets");
+  PartArgs a;
+  memset(&a, 0, sizeof(a));
+  a.pid_in = pid;
+  a.n = nrows;
+  a.P = P;
+  a.pow2 = (P & (P - 1)) == 0;
+  a.rounds = pick_rounds(nrows, P);
+  a.ntiles = nrows == 0 ? 0 : div_up(nrows, (int64_t)a.rounds * 32);
+  const int64_t ncounters = a.ntiles * P;
+  if (ncounters > kStaticMaxCounters)
+    return fail(CYL_CapacityError,
+                "cyl_scatter_map_static: %lld rows x %u partitions need %lld counters, the static scratch holds %lld "
+                "(about %lld rows at this partition count); use cyl_scatter_map for larger inputs",
+                (long long)nrows, P, (long long)ncounters, (long long)kStaticMaxCounters,
+                (long long)(kStaticMaxCounters / P * a.rounds * 32));
+  StaticScatterScratch *ws = nullptr;
+  CYL_TRY(static_scatter_scratch(&ws));  // first call on a device resolves the symbol address
+  if (nrows == 0) {
+    CYL_CUDA(cudaMemsetAsync(part_offsets, 0, (P + 1) * sizeof(int64_t), s));
+    return CYL_OK;
+  }
+  // Every word of the scratch that is read below is written first by this call (each tile stores all P of its
+  // counters, the scans overwrite their outputs), so nothing left behind by an earlier call can leak in.
+  a.tile_hist = ws->hist;
+  CYL_TRY(launch_part<PM_TILE_HIST>(a, (size_t)kPartWarps * P * sizeof(uint32_t), s));
+  CYL_TRY(exclusive_scan_u32_in_workspace(ws->hist, ncounters, ws->base, ws->scan_tiles, s));
+  extract_part_offsets<<<(P + 1 + 255) / 256, 256, 0, s>>>(ws->base, a.ntiles, P, part_offsets);
+  CYL_LAUNCH_CHECK();
+  a.tile_base = ws->base;
+  a.dest = dest;
+  CYL_TRY(launch_part<PM_DEST>(a, (size_t)kPartWarps * P * sizeof(int64_t), s));
+  return CYL_OK;
 }
 
 int cyl_partition_map(const cyl_column_t *cols, int32_t ncols, int64_t nrows, uint32_t P, uint32_t *pid_out, int64_t *dest,

@@ -99,6 +99,20 @@ int exclusive_scan(const T *in, int64_t n, int64_t *out, cudaStream_t stream) {
   return CYL_OK;
 }
 
+// Same scan, but the tile-sum workspace (div_up(n, kScanTile) int64 values) is supplied by the caller: nothing is
+// allocated. Used by the entry point that must not allocate.
+int exclusive_scan_u32_in_workspace(const uint32_t *in, int64_t n, int64_t *out, int64_t *tile_workspace, cudaStream_t stream) {
+  if (n <= 0) return fail(CYL_Invalid, "exclusive_scan_u32_in_workspace: empty input");
+  const int64_t ntiles = div_up(n, kScanTile);
+  scan_tile_reduce<uint32_t><<<(unsigned)ntiles, kScanThreads, 0, stream>>>(in, n, tile_workspace);
+  CYL_LAUNCH_CHECK();
+  scan_tile_sums<<<1, 1024, 0, stream>>>(tile_workspace, ntiles, out + n);
+  CYL_LAUNCH_CHECK();
+  scan_tile_write<uint32_t><<<(unsigned)ntiles, kScanThreads, 0, stream>>>(in, n, tile_workspace, out);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
 template int exclusive_scan<int64_t>(const int64_t *, int64_t, int64_t *, cudaStream_t);
 template int exclusive_scan<uint32_t>(const uint32_t *, int64_t, int64_t *, cudaStream_t);
 template int exclusive_scan<int32_t>(const int32_t *, int64_t, int64_t *, cudaStream_t);

@@ -38,4 +38,7 @@ __device__ __forceinline__ int64_t warp_reduce_sum(int64_t v) {
 template <typename T>
 int exclusive_scan(const T *in, int64_t n, int64_t *out, cudaStream_t stream);
 
+// non-allocating form: tile_workspace holds div_up(n, kScanTile) int64 values supplied by the caller
+int exclusive_scan_u32_in_workspace(const uint32_t *in, int64_t n, int64_t *out, int64_t *tile_workspace, cudaStream_t stream);
+
 }  // namespace cylb

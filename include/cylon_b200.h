@@ -67,6 +67,26 @@ int cyl_hash_partition(const cyl_column_t *cols /* host array */, int32_t ncols,
  * Replaces the row routing of ArrowArraySplitKernel::Split (arrow/arrow_kernels.cpp:40-72). */
 int cyl_scatter_map(const uint32_t *pid, int64_t nrows, uint32_t num_partitions, int64_t *dest, int64_t *part_offsets,
                     void *stream);
+/* cyl_scatter_map for callers that are not allowed to allocate device memory. (No counterpart in the reference.)
+ * Who that is: an engine that hands the whole GPU to its own arena at start-up, so a later cudaMalloc either fails or
+ * breaks its memory accounting; or a latency-bound service whose policy forbids allocator calls on the request path
+ * because they can stall behind other work on the device. cyl_scatter_map takes its scratch (per-tile histograms,
+ * their scanned cursors, the scan's tile sums) from the stream-ordered pool; this variant keeps the same scratch in a
+ * fixed 3.0 MB array that is part of the library image, so it calls no cudaMalloc/cudaFree/cudaMallocAsync (or any
+ * other allocating routine) at all. Inputs and outputs are still the caller's buffers, and the results are identical
+ * to cyl_scatter_map's.
+ * Limits and rules:
+ *   - tiles x partitions must fit the array: ceil(nrows / tile_rows) * num_partitions <= 262144 counters, where
+ *     tile_rows = 1024 for num_partitions <= 128 (and grows with it). That is about 33.5 million rows at 8
+ *     partitions, 4.1 million at 64. Larger inputs are rejected with CYL_CapacityError and a message saying so.
+ *   - the array exists once per GPU that loaded the library and is held until the process exits.
+ *   - the first call on each device looks up the array's device address (with that device current); make that first
+ *     call before starting any stream capture.
+ *   - all calls on a device share the array. A call overwrites every word it later reads, so stale contents from an
+ *     earlier call are harmless, but two calls that can run on the GPU at the same time (different streams or host
+ *     threads) race on it: serialise them. */
+int cyl_scatter_map_static(const uint32_t *pid, int64_t nrows, uint32_t num_partitions, int64_t *dest, int64_t *part_offsets,
+                           void *stream);
 /* Same, with pid computed on the fly from the key columns (fuses cyl_hash_partition + cyl_scatter_map;
  * pid_out may be NULL). */
 int cyl_partition_map(const cyl_column_t *cols /* host array */, int32_t ncols, int64_t nrows, uint32_t num_partitions,
