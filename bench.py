@@ -41,14 +41,17 @@ def synth_table(rows, key_range, seed, rank, out_keys=None, out_vals=None, chunk
     """(int64 key uniform in [0, key_range), double payload in [DBL_MIN, 1)); deterministic in (seed, rank, row)."""
     keys = out_keys if out_keys is not None else np.empty(rows, dtype=np.int64)
     vals = out_vals if out_vals is not None else np.empty(rows, dtype=np.float64)
-    base = np.uint64((seed * 1000003 + rank * 7919) & 0xFFFFFFFFFFFFFFFF)
+    # one independent counter-based stream per (seed, rank, column): random 64-bit start, then consecutive counters
+    kbase = splitmix64(np.array([seed * 4096 + rank * 2 + 0], dtype=np.uint64))[0]
+    vbase = splitmix64(np.array([seed * 4096 + rank * 2 + 1], dtype=np.uint64))[0]
     tiny = np.finfo(np.float64).tiny
     for s in range(0, rows, chunk):
         e = min(rows, s + chunk)
         with np.errstate(over="ignore"):
-            i = np.arange(s, e, dtype=np.uint64) * np.uint64(2) + base
-        keys[s:e] = (splitmix64(i) % np.uint64(key_range)).astype(np.int64)
-        v = (splitmix64(i + np.uint64(1)) >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+            i = np.arange(s, e, dtype=np.uint64)
+            ki, vi = i + kbase, i + vbase
+        keys[s:e] = (splitmix64(ki) % np.uint64(key_range)).astype(np.int64)
+        v = (splitmix64(vi) >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
         np.maximum(v, tiny, out=v)
         vals[s:e] = v
     return keys, vals

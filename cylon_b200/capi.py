@@ -372,3 +372,22 @@ def profile_report():
         name, n, ms = line.rsplit(",", 2)
         out[name] = (int(n), float(ms))
     return out
+
+
+def hash_join_fused(lcols, lkey, rcols, rkey, capacity=None, stream=None):
+    """cyl_hash_join_fused_inner through the C-ABI -> (list of DCol output columns, rows, attempts)."""
+    nl, nr = lcols[0].length, rcols[0].length
+    if capacity is None:
+        capacity = max(nl, nr) + max(nl, nr) // 8 + 1024
+    attempts = 0
+    while True:
+        attempts += 1
+        outs = [DeviceBuffer(max(1, capacity * c.byte_width)) for c in list(lcols) + list(rcols)]
+        ptrs = (C.c_void_p * len(outs))(*[o.ptr for o in outs])
+        m = C.c_int64()
+        check(lib().cyl_hash_join_fused_inner(c_columns(lcols), len(lcols), C.c_int32(lkey), c_columns(rcols), len(rcols), C.c_int32(rkey),
+                                              C.c_int64(nl), C.c_int64(nr), C.c_int64(capacity), ptrs, C.byref(m), C.c_void_p(stream)))
+        if m.value <= capacity:
+            cols = [DCol(c.type, m.value, o, byte_width=c.byte_width, name=c.name) for c, o in zip(list(lcols) + list(rcols), outs)]
+            return cols, m.value, attempts
+        capacity = m.value

@@ -5,6 +5,8 @@
 // control flow is the reference's; every data-touching step is a CUDA kernel reached through the C-ABI.
 #include "cylon/table.hpp"
 
+#include <algorithm>
+
 #include "table_ops.hpp"
 
 namespace cylon {
@@ -155,6 +157,40 @@ Status Join(std::shared_ptr<Table> &left, std::shared_ptr<Table> &right, const j
   void *stream = ctx->GetStream();
   const auto lk = detail::Descs(*left, lidx), rk = detail::Descs(*right, ridx);
   const int jt = (int)cfg.GetType();
+
+  // fast path: radix-partitioned shared-memory join that writes the result columns directly
+  if (cfg.GetAlgorithm() == join::config::HASH && lidx.size() == 1 && ctx->GetConfig("cylon.join.fused", "1") != "0") {
+    const auto lall = detail::AllDescs(*left), rall = detail::AllDescs(*right);
+    if (cyl_hash_join_fused_supported(lall.data(), (int32_t)lall.size(), lidx[0], rall.data(), (int32_t)rall.size(), ridx[0], jt)) {
+      const int64_t nl = left->Rows(), nr = right->Rows();
+      int64_t capacity = std::max(nl, nr) + std::max(nl, nr) / 8 + 1024;
+      for (int attempt = 0; attempt < 2; attempt++) {
+        std::vector<std::shared_ptr<Column>> cols;
+        std::vector<void *> outs;
+        for (int side = 0; side < 2; side++) {
+          const Table &t = side == 0 ? *left : *right;
+          const std::string &prefix = side == 0 ? cfg.GetLeftTableSuffix() : cfg.GetRightTableSuffix();
+          for (const auto &src : t.GetColumns()) {
+            std::shared_ptr<Column> col;
+            RETURN_CYLON_STATUS_IF_FAILED(
+                Column::Allocate(prefix + src->name(), src->type(), src->byte_width(), capacity, capacity * (int64_t)src->byte_width(), false, stream, &col));
+            outs.push_back(col->mutable_data());
+            cols.push_back(col);
+          }
+        }
+        int64_t m = 0;
+        CYL_RETURN_IF_FAILED(cyl_hash_join_fused_inner(lall.data(), (int32_t)lall.size(), lidx[0], rall.data(), (int32_t)rall.size(), ridx[0], nl, nr,
+                                                       capacity, outs.data(), &m, stream));
+        if (m <= capacity) {
+          for (auto &c : cols) c->truncate(m);
+          out = std::make_shared<Table>(std::move(cols), ctx);
+          return Status::OK();
+        }
+        capacity = m;  // the optimistic capacity was too small: the exact size is known now
+      }
+      return Status(Code::ExecutionError, "fused join did not fit its exact capacity");
+    }
+  }
 
   cyl_join_plan_t *plan = nullptr;
   int64_t m = 0;

@@ -39,6 +39,11 @@ class Column {
   int32_t *mutable_offsets() { return const_cast<int32_t *>(desc_.offsets); }
   void *mutable_data() { return const_cast<void *>(desc_.data); }
   void drop_validity();  // frees the bitmap (all rows valid)
+  // fixed-width columns only: keep the first `rows` rows of a buffer that was allocated with spare capacity
+  void truncate(int64_t rows) {
+    desc_.length = rows;
+    data_bytes_ = rows * (int64_t)desc_.byte_width;
+  }
 
   // device -> host copies into caller buffers sized by length()/data_bytes(); any pointer may be null to skip
   Status ToHost(void *data, int32_t *offsets, uint8_t *validity, void *stream) const;

@@ -132,6 +132,22 @@ int cyl_sort_join_count(const cyl_column_t *lkeys /* host array */, const cyl_co
 int cyl_join_materialize(cyl_join_plan_t *plan, int64_t *l_idx, int64_t *r_idx, void *stream);
 void cyl_join_plan_free(cyl_join_plan_t *plan);
 
+/* Fused fast path of the INNER hash join: radix-partition both tables on the key hash, then build each partition's
+ * hash table in SHARED memory and write the joined rows directly (no index vectors, no gather pass). Requirements
+ * (cyl_hash_join_fused_supported returns 1): INNER, one key column per side of the same fixed-width type (<= 8 bytes),
+ * every column fixed width (1/2/4/8 bytes) without a validity bitmap, at most 8 columns per side.
+ * out_cols: host array of nlcols + nrcols device pointers (left columns first, the layout build_final_table produces,
+ * join/join_utils.cpp:126-181), each with room for `capacity` values. The result size is only known after probing:
+ * *num_rows (host out; the call synchronises) always receives the exact count; the rows were written only if
+ * *num_rows <= capacity, otherwise repeat the call with capacity >= *num_rows. Row order is unspecified.
+ * Replaces ArrayIndexHashJoin + build_final_table + copy_array_by_indices (join/hash_join.cpp:188-307,
+ * join/join_utils.cpp:126-181, util/copy_arrray.cpp:24-50). */
+int cyl_hash_join_fused_supported(const cyl_column_t *lcols /* host array */, int32_t nlcols, int32_t lkey, const cyl_column_t *rcols /* host array */,
+                                  int32_t nrcols, int32_t rkey, int32_t join_type);
+int cyl_hash_join_fused_inner(const cyl_column_t *lcols /* host array */, int32_t nlcols, int32_t lkey, const cyl_column_t *rcols /* host array */,
+                              int32_t nrcols, int32_t rkey, int64_t nl, int64_t nr, int64_t capacity, void *const *out_cols /* host array */,
+                              int64_t *num_rows /* host out */, void *stream);
+
 /* ---------------------------------------------------------------- D4: gather ------------------- */
 /* dst[i] = idx[i] < 0 ? 0 : src[idx[i]]; dst_validity (may be NULL) gets bit i = (idx[i] >= 0), it has
  * ceil(m/32)*4 bytes. Source validity is not propagated, as in the reference.

@@ -48,9 +48,11 @@ def synth_kv(nrows, key_range, seed, rank=0):
     """(int64 key uniform in [0, key_range), double payload in [DBL_MIN, 1)) -- SURVEY.md 8(d)."""
     with np.errstate(over="ignore"):
         i = np.arange(nrows, dtype=np.uint64)
-        base = np.uint64((seed * 1000003 + rank * 7919) & 0xFFFFFFFFFFFFFFFF)
-        k = splitmix64(i * np.uint64(2) + base)
-        v = splitmix64(i * np.uint64(2) + np.uint64(1) + base)
+        # one independent stream per (seed, rank, column)
+        kbase = splitmix64(np.array([seed * 4096 + rank * 2 + 0], dtype=np.uint64))[0]
+        vbase = splitmix64(np.array([seed * 4096 + rank * 2 + 1], dtype=np.uint64))[0]
+        k = splitmix64(i + kbase)
+        v = splitmix64(i + vbase)
     keys = (k % np.uint64(key_range)).astype(np.int64)
     vals = (v >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
     vals = np.maximum(vals, np.finfo(np.float64).tiny)
