@@ -113,6 +113,10 @@ def algorithmic_bytes(kernel, n, m):
         "hash_join_scan": n * 4 + n * 8,     # counts in, offsets out
         "hash_join_init_slots": 0,
         "gather_fixed": m * 8 + m * 8,       # per launch: one 8-byte column, values in + out
+        "fused_join_hist": n * 8,            # per launch (one table): keys in
+        "fused_join_offsets": 0,
+        "fused_join_scatter": n * 16 * 2,    # per launch (one table): (key, payload) columns in + packed records out
+        "fused_join_probe": 2 * n * 16 + m * 32,  # both record streams in + the 4 result columns out (= SURVEY 8d local join)
         "partition_tile_hist": n * 8,
         "partition_scatter": n * 16 * 2,     # whole (key, payload) table in + out
         "partition_scan": 0,

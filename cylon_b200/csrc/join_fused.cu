@@ -20,6 +20,7 @@
 // Bins larger than the shared-memory budget (key skew) are processed in several build chunks, which is exact for an
 // inner join. Output order is unspecified (row multiset == reference).
 #include "common.cuh"
+#include "join_fused.cuh"
 #include "scan.cuh"
 
 namespace cylb {
@@ -245,7 +246,7 @@ static bool plan_smem(const cyl_column_t *bcols, int nb_cols, FusedPlan *pl) {
   int row_bytes = 0;
   for (int c = 0; c < nb_cols; c++) row_bytes += bcols[c].byte_width;
   const int budget = 100 * 1024;  // two CTAs per SM
-  int cap = budget / (row_bytes + 2 + 8);
+  int cap = budget / (row_bytes + 2 + 16);  // 16 = worst-case bytes of heads per row (nheads < 4 * cap)
   cap = cap / 256 * 256;
   if (cap > 16384) cap = 16384;  // next links are 16-bit, 0xFFFF is the end marker
   if (cap < 256) return false;
@@ -345,6 +346,9 @@ int cyl_hash_join_fused_inner(const cyl_column_t *lcols, int32_t nlcols, int32_t
   const int64_t nb = build_left ? nl : nr, np = build_left ? nr : nl;
   void *const *bout = build_left ? out_cols : out_cols + nlcols;
   void *const *pout = build_left ? out_cols + nlcols : out_cols;
+
+  if (fused8_eligible(lcols, nlcols, rcols, nrcols))  // all columns 8 bytes wide: packed-record kernels (join_fused8.cu)
+    return fused8_join(bcols, nbc, bkey, nb, pcols, npc, pkey, np, bout, pout, capacity, num_rows, s);
 
   FusedPlan pl;
   plan_smem(bcols, nbc, &pl);

@@ -1,0 +1,11 @@
+// join_fused.cuh -- shared declarations of the fused join paths (join_fused.cu generic widths, join_fused8.cu all-8-byte).
+#pragma once
+#include "common.cuh"
+
+namespace cylb {
+constexpr int kFused8MaxCols = 4;
+bool fused8_eligible(const cyl_column_t *lcols, int nlcols, const cyl_column_t *rcols, int nrcols);
+// build side b*, probe side p*; bout/pout: output column pointers of each side (capacity rows each)
+int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const cyl_column_t *pcols, int npc, int pkey, int64_t np,
+                void *const *bout, void *const *pout, int64_t capacity, int64_t *num_rows, cudaStream_t s);
+}  // namespace cylb
