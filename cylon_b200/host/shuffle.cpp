@@ -215,6 +215,31 @@ Status HashPartition(std::shared_ptr<Table> &table, const std::vector<int> &hash
 }
 
 // ---------------------------------------------------------------------------------------------- shuffle
+}  // namespace cylon
+
+// Pure host arithmetic of the all-to-all (no GPU, no communicator): counts[src * world + dst] = units (rows or bytes)
+// that rank `src` sends to rank `dst`, as every rank knows after the count exchange. For `rank` it yields where each
+// peer's slice starts in its partition-ordered send buffer and in its receive buffer (chunks ordered by source rank).
+extern "C" int cyl_shuffle_plan(const int64_t *counts, int32_t world, int32_t rank, int64_t *send_off, int64_t *send_cnt, int64_t *recv_off,
+                                int64_t *recv_cnt, int64_t *total_recv) {
+  if (!counts || world < 1 || rank < 0 || rank >= world) return CYL_Invalid;
+  int64_t so = 0, ro = 0;
+  for (int p = 0; p < world; p++) {
+    const int64_t s = counts[(int64_t)rank * world + p], r = counts[(int64_t)p * world + rank];
+    if (s < 0 || r < 0) return CYL_Invalid;
+    send_off[p] = so;
+    send_cnt[p] = s;
+    so += s;
+    recv_off[p] = ro;
+    recv_cnt[p] = r;
+    ro += r;
+  }
+  if (total_recv) *total_recv = ro;
+  return CYL_OK;
+}
+
+namespace cylon {
+
 static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &table, const std::vector<int> &hash_cols,
                                std::shared_ptr<Table> &out) {
   auto comm = ctx->GetCommunicator();
@@ -242,13 +267,15 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
   RETURN_CYLON_STATUS_IF_FAILED(comm->AllGather(mine.data(), nvec, all.data(), stream));
   auto at = [&](int src, int field) { return all[(size_t)src * nvec + field]; };
 
-  // ---- receive layout: chunks ordered by source rank
-  std::vector<int64_t> recv_rows(P), recv_row_off(P + 1, 0);
-  for (int sr = 0; sr < P; sr++) {
-    recv_rows[sr] = at(sr, rank);
-    recv_row_off[sr + 1] = recv_row_off[sr] + recv_rows[sr];
-  }
-  const int64_t total_rows = recv_row_off[P];
+  // ---- receive layout: chunks ordered by source rank (cyl_shuffle_plan)
+  std::vector<int64_t> row_matrix((size_t)P * P);
+  for (int sr = 0; sr < P; sr++)
+    for (int d = 0; d < P; d++) row_matrix[(size_t)sr * P + d] = at(sr, d);
+  std::vector<int64_t> recv_rows(P), recv_row_off(P + 1, 0), plan_send_off(P), plan_send_cnt(P);
+  int64_t total_rows = 0;
+  CYL_RETURN_IF_FAILED(cyl_shuffle_plan(row_matrix.data(), P, rank, plan_send_off.data(), plan_send_cnt.data(), recv_row_off.data(),
+                                        recv_rows.data(), &total_rows));
+  recv_row_off[P] = total_rows;
   if (total_rows > 0xFFFFFFFEll) return Status(Code::CapacityError, "shuffle would put more than 2^32-2 rows on one GPU");
 
   std::vector<std::shared_ptr<Column>> out_cols((size_t)ncols);

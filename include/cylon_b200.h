@@ -211,6 +211,16 @@ int cyl_pack_validity(const uint8_t *bytes, int64_t n, uint8_t *bitmap, void *st
 int cyl_offsets_to_lengths(const int32_t *offsets, int64_t n, int32_t *lengths, void *stream);
 int cyl_lengths_to_offsets(const int32_t *lengths, int64_t n, int32_t *offsets, int64_t *total_bytes /* host out */, void *stream);
 
+/* ---------------------------------------------------------------- C: shuffle plan -------------- */
+/* Host-only arithmetic of the all-to-all (all pointers are HOST pointers; no GPU needed): counts[src * world + dst] =
+ * units (rows or bytes) rank src sends to rank dst, known to every rank after the count exchange. For `rank`: where
+ * each peer's slice starts / how long it is in the partition-ordered send buffer (send_off, send_cnt) and in the
+ * receive buffer, whose chunks are ordered by source rank (recv_off, recv_cnt); *total_recv = rows/bytes received.
+ * Replaces the per-buffer header/FIN handshake and the receive-side allocation of
+ * arrow/arrow_all_to_all.cpp:68-211 + net/ops/all_to_all.cpp:78-137 with offsets known before any payload moves. */
+int cyl_shuffle_plan(const int64_t *counts /* host */, int32_t world, int32_t rank, int64_t *send_off, int64_t *send_cnt, int64_t *recv_off,
+                     int64_t *recv_cnt, int64_t *total_recv);
+
 /* ---------------------------------------------------------------- checks ----------------------- */
 /* Order-independent checksum of a table: sum over rows of a 64-bit mix of the row's values (nulls count as
  * zero bits + validity 0). No counterpart in the reference; it is how full-size results are compared with the
