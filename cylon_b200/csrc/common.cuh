@@ -47,7 +47,16 @@ struct ProfScope {
   ~ProfScope();
 };
 
-// Stream-ordered scratch buffer (cudaMallocAsync from the device's default pool; freed on the same stream).
+// Caching device allocator behind every buffer the library creates (scratch, join plans, table columns). Blocks are
+// rounded to a size class and, when released, parked on a free list keyed by (device, stream, class); a block is only
+// handed out again for work on the SAME stream, so stream order makes the reuse safe without events. After warm-up no
+// call reaches cudaMalloc/cudaFree. (cudaMallocAsync's pool was measured to spend ~40 ms per step re-mapping physical
+// memory once the allocation sizes of the shuffle and the join interleave.)
+cudaError_t pool_malloc(void **ptr, size_t bytes, cudaStream_t stream);
+cudaError_t pool_free(void *ptr, cudaStream_t stream);
+void pool_trim();  // cudaFree every parked block
+
+// Stream-ordered scratch buffer from that allocator.
 struct Scratch {
   void *p = nullptr;
   cudaStream_t s = nullptr;

@@ -153,7 +153,7 @@ void plan_release(cyl_join_plan *p) {
   if (!p) return;
   void *ptrs[] = {p->table, p->next, p->pslot, p->out_off, p->bsurv, p->bsurv_pos, p->lperm, p->rperm, p->lo, p->hi, p->rsurv, p->rsurv_pos};
   for (void *q : ptrs)
-    if (q) cudaFreeAsync(q, p->stream);
+    if (q) pool_free(q, p->stream);
   delete p;
 }
 

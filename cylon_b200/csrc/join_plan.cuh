@@ -35,8 +35,8 @@ int sort_join_materialize(cyl_join_plan *p, int64_t *l_idx, int64_t *r_idx, cuda
 template <typename T>
 int plan_alloc(T **ptr, size_t count, cudaStream_t s) {
   void *q = nullptr;
-  cudaError_t e = cudaMallocAsync(&q, (count ? count : 1) * sizeof(T), s);
-  if (e != cudaSuccess) return cuda_fail(e, "cudaMallocAsync(join plan)", __FILE__, __LINE__);
+  cudaError_t e = pool_malloc(&q, (count ? count : 1) * sizeof(T), s);
+  if (e != cudaSuccess) return cuda_fail(e, "pool_malloc(join plan)", __FILE__, __LINE__);
   *ptr = static_cast<T *>(q);
   return CYL_OK;
 }

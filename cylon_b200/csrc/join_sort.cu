@@ -231,7 +231,7 @@ static int sort_side(const DCols &k, int64_t n, bool exact, Scratch *tags_a, Scr
   CYL_TRY(plan_alloc(&ids_a, (size_t)n + 1, s));
   int rc = plan_alloc(&ids_b, (size_t)n + 1, s);
   if (rc != CYL_OK) {
-    cudaFreeAsync(ids_a, s);
+    pool_free(ids_a, s);
     return rc;
   }
   uint64_t *ta = tags_a->as<uint64_t>(), *tb = tags_b->as<uint64_t>();
@@ -241,9 +241,9 @@ static int sort_side(const DCols &k, int64_t n, bool exact, Scratch *tags_a, Scr
     if (e != cudaSuccess) rc = cuda_fail(e, "make_tags_kernel", __FILE__, __LINE__);
   }
   if (rc == CYL_OK) rc = radix_sort_pairs(&ta, &ids_a, &tb, &ids_b, n, s);
-  cudaFreeAsync(ids_b, s);
+  pool_free(ids_b, s);
   if (rc != CYL_OK) {
-    cudaFreeAsync(ids_a, s);
+    pool_free(ids_a, s);
     return rc;
   }
   *perm_out = ids_a;

@@ -53,10 +53,10 @@ int RowTableHost::alloc(int64_t capacity, cudaStream_t stream) {
   s = stream;
   cap = capacity;
   void *p = nullptr;
-  CYL_CUDA(cudaMallocAsync(&p, (size_t)(cap + 1) * sizeof(RSlot) + 64, s));
+  CYL_CUDA(pool_malloc(&p, (size_t)(cap + 1) * sizeof(RSlot) + 64, s));
   t.slots = static_cast<RSlot *>(p);
   void *q = nullptr;
-  CYL_CUDA(cudaMallocAsync(&q, 64, s));
+  CYL_CUDA(pool_malloc(&q, 64, s));
   t.nclaimed = static_cast<unsigned long long *>(q);
   t.flags = reinterpret_cast<int *>(static_cast<char *>(q) + 16);
   t.mask = (unsigned long long)cap - 1;
@@ -68,8 +68,8 @@ int RowTableHost::alloc(int64_t capacity, cudaStream_t stream) {
 }
 
 void RowTableHost::release() {
-  if (t.slots) cudaFreeAsync(t.slots, s);
-  if (t.nclaimed) cudaFreeAsync(t.nclaimed, s);
+  if (t.slots) pool_free(t.slots, s);
+  if (t.nclaimed) pool_free(t.nclaimed, s);
   t.slots = nullptr;
   t.nclaimed = nullptr;
 }

@@ -28,21 +28,94 @@ int cuda_fail(cudaError_t e, const char *expr, const char *file, int line) {
   return e == cudaErrorMemoryAllocation ? CYL_OutOfMemory : CYL_ExecutionError;
 }
 
+// ---- caching allocator ------------------------------------------------------------------------------------------
+namespace {
+struct PoolKey {
+  int dev;
+  cudaStream_t stream;
+  size_t cls;
+  bool operator<(const PoolKey &o) const {
+    if (dev != o.dev) return dev < o.dev;
+    if (stream != o.stream) return stream < o.stream;
+    return cls < o.cls;
+  }
+};
+std::mutex g_pool_mu;
+std::map<PoolKey, std::vector<void *>> g_pool_free;
+std::map<void *, std::pair<int, size_t>> g_pool_live;  // ptr -> (device, class)
+
+size_t size_class(size_t bytes) {
+  if (bytes < 512) return 512;
+  // keep the top 3 bits after the leading one: classes are at most 12.5 % larger than the request
+  int lead = 63 - __builtin_clzll((unsigned long long)bytes);
+  const size_t step = (size_t)1 << (lead > 3 ? lead - 3 : 0);
+  return (bytes + step - 1) / step * step;
+}
+}  // namespace
+
+void pool_trim() {
+  std::lock_guard<std::mutex> lk(g_pool_mu);
+  for (auto &kv : g_pool_free)
+    for (void *p : kv.second) {
+      cudaFree(p);
+      g_pool_live.erase(p);
+    }
+  g_pool_free.clear();
+}
+
+cudaError_t pool_malloc(void **ptr, size_t bytes, cudaStream_t stream) {
+  *ptr = nullptr;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const size_t cls = size_class(bytes);
+  {
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    auto it = g_pool_free.find(PoolKey{dev, stream, cls});
+    if (it != g_pool_free.end() && !it->second.empty()) {
+      *ptr = it->second.back();
+      it->second.pop_back();
+      return cudaSuccess;
+    }
+  }
+  void *p = nullptr;
+  e = cudaMalloc(&p, cls);
+  if (e == cudaErrorMemoryAllocation) {  // give parked blocks back to the driver and try once more
+    (void)cudaGetLastError();
+    pool_trim();
+    e = cudaMalloc(&p, cls);
+  }
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lk(g_pool_mu);
+  g_pool_live[p] = std::make_pair(dev, cls);
+  *ptr = p;
+  return cudaSuccess;
+}
+
+cudaError_t pool_free(void *ptr, cudaStream_t stream) {
+  if (!ptr) return cudaSuccess;
+  std::lock_guard<std::mutex> lk(g_pool_mu);
+  auto it = g_pool_live.find(ptr);
+  if (it == g_pool_live.end()) return cudaFree(ptr);  // not ours
+  g_pool_free[PoolKey{it->second.first, stream, it->second.second}].push_back(ptr);
+  return cudaSuccess;
+}
+
 int Scratch::alloc(size_t bytes, cudaStream_t stream) {
   release();
   s = stream;
   if (bytes == 0) bytes = 16;
-  cudaError_t e = cudaMallocAsync(&p, bytes, stream);
+  cudaError_t e = pool_malloc(&p, bytes, stream);
   if (e != cudaSuccess) {
     p = nullptr;
-    return cuda_fail(e, "cudaMallocAsync(scratch)", __FILE__, __LINE__);
+    return cuda_fail(e, "pool_malloc(scratch)", __FILE__, __LINE__);
   }
   return CYL_OK;
 }
 
 void Scratch::release() {
   if (p) {
-    cudaFreeAsync(p, s);
+    pool_free(p, s);
     p = nullptr;
   }
 }
@@ -249,3 +322,18 @@ int cyl_host_free_pinned(void *ptr) {
 }
 
 }  // extern "C"
+
+// C-ABI doors onto the caching allocator (for hosts that want their table buffers to come from the same pool)
+extern "C" int cyl_pool_alloc(void **ptr, int64_t bytes, void *stream) {
+  if (bytes < 0) return cylb::fail(CYL_Invalid, "cyl_pool_alloc: negative size");
+  CYL_CUDA(cylb::pool_malloc(ptr, (size_t)bytes, (cudaStream_t)stream));
+  return CYL_OK;
+}
+extern "C" int cyl_pool_free(void *ptr, void *stream) {
+  CYL_CUDA(cylb::pool_free(ptr, (cudaStream_t)stream));
+  return CYL_OK;
+}
+extern "C" int cyl_pool_trim(void) {
+  cylb::pool_trim();
+  return CYL_OK;
+}

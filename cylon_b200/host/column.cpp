@@ -10,13 +10,13 @@ namespace cylon {
 Column::~Column() {
   if (!owns_) return;
   cudaStream_t s = static_cast<cudaStream_t>(stream_);
-  if (desc_.validity) cudaFreeAsync(const_cast<uint8_t *>(desc_.validity), s);
-  if (desc_.offsets) cudaFreeAsync(const_cast<int32_t *>(desc_.offsets), s);
-  if (desc_.data) cudaFreeAsync(const_cast<void *>(desc_.data), s);
+  if (desc_.validity) cylb::pool_free(const_cast<uint8_t *>(desc_.validity), s);
+  if (desc_.offsets) cylb::pool_free(const_cast<int32_t *>(desc_.offsets), s);
+  if (desc_.data) cylb::pool_free(const_cast<void *>(desc_.data), s);
 }
 
 void Column::drop_validity() {
-  if (owns_ && desc_.validity) cudaFreeAsync(const_cast<uint8_t *>(desc_.validity), static_cast<cudaStream_t>(stream_));
+  if (owns_ && desc_.validity) cylb::pool_free(const_cast<uint8_t *>(desc_.validity), static_cast<cudaStream_t>(stream_));
   desc_.validity = nullptr;
   desc_.null_count = 0;
 }
@@ -34,14 +34,14 @@ Status Column::Allocate(const std::string &name, int32_t type, int32_t byte_widt
   c->desc_.null_count = with_validity ? -1 : 0;  // -1 = unknown, as Arrow allows
   c->data_bytes_ = data_bytes;
   void *p = nullptr;
-  CUDA_RETURN_IF_FAILED(cudaMallocAsync(&p, data_bytes > 0 ? (size_t)data_bytes : 16, s));
+  CUDA_RETURN_IF_FAILED(cylb::pool_malloc(&p, data_bytes > 0 ? (size_t)data_bytes : 16, s));
   c->desc_.data = p;
   if (type == CYL_STRING || type == CYL_BINARY) {
-    CUDA_RETURN_IF_FAILED(cudaMallocAsync(&p, (size_t)(length + 1) * sizeof(int32_t), s));
+    CUDA_RETURN_IF_FAILED(cylb::pool_malloc(&p, (size_t)(length + 1) * sizeof(int32_t), s));
     c->desc_.offsets = static_cast<int32_t *>(p);
   }
   if (with_validity) {
-    CUDA_RETURN_IF_FAILED(cudaMallocAsync(&p, detail::validity_bytes(length), s));
+    CUDA_RETURN_IF_FAILED(cylb::pool_malloc(&p, detail::validity_bytes(length), s));
     c->desc_.validity = static_cast<uint8_t *>(p);
   }
   *out = c;

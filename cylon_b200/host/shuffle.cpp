@@ -247,8 +247,10 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
   void *stream = ctx->GetStream();
   const int ncols = table->Columns();
 
+  detail::StageTrace trace("shuffle", stream);
   Partitioned pt;
   RETURN_CYLON_STATUS_IF_FAILED(PartitionTable(table, hash_cols, (uint32_t)P, &pt));
+  trace.mark("partition");
   std::vector<std::string> names = table->ColumnNames();
   std::vector<int> has_validity(ncols);
   for (int c = 0; c < ncols; c++) has_validity[c] = table->GetColumn(c)->has_validity() ? 1 : 0;
@@ -265,6 +267,7 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
     for (int p = 0; p < P; p++) mine[P * (1 + v) + p] = pt.byte_off[var_cols[v]][p + 1] - pt.byte_off[var_cols[v]][p];
   for (int c = 0; c < ncols; c++) mine[P * (1 + var_cols.size()) + c] = has_validity[c];
   RETURN_CYLON_STATUS_IF_FAILED(comm->AllGather(mine.data(), nvec, all.data(), stream));
+  trace.mark("count exchange");
   auto at = [&](int src, int field) { return all[(size_t)src * nvec + field]; };
 
   // ---- receive layout: chunks ordered by source rank (cyl_shuffle_plan)
@@ -353,7 +356,9 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
     posts.push_back(post);
   }
 
+  trace.mark("allocate outputs");
   RETURN_CYLON_STATUS_IF_FAILED(comm->AllToAllV(ex, stream));
+  trace.mark("all-to-all");
 
   for (const auto &post : posts) {
     if (post.lens)
@@ -390,8 +395,12 @@ Status DistributedJoin(std::shared_ptr<Table> &left, std::shared_ptr<Table> &rig
   RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*left, cfg.GetLeftColumnIdx(), "DistributedJoin(left)"));
   RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*right, cfg.GetRightColumnIdx(), "DistributedJoin(right)"));
   std::shared_ptr<Table> l, r;
+  detail::StageTrace trace("DistributedJoin", ctx->GetStream());
   RETURN_CYLON_STATUS_IF_FAILED(ShuffleTwo(ctx, left, cfg.GetLeftColumnIdx(), right, cfg.GetRightColumnIdx(), l, r));
-  return Join(l, r, cfg, out);
+  trace.mark("shuffle both tables");
+  Status st = Join(l, r, cfg, out);
+  trace.mark("local join");
+  return st;
 }
 
 typedef Status (*LocalSetOperation)(std::shared_ptr<Table> &, std::shared_ptr<Table> &, std::shared_ptr<Table> &);

@@ -39,6 +39,13 @@ int cyl_memcpy_d2d(void *dst, const void *src, int64_t bytes, void *stream);
 int cyl_stream_sync(void *stream);
 int cyl_host_alloc_pinned(void **ptr /* host out */, int64_t bytes);
 int cyl_host_free_pinned(void *ptr);
+/* The library's caching device allocator (every scratch buffer, join plan and table column comes from it): blocks are
+ * parked per (device, stream, size class) when released and only reused for work on the same stream, so after warm-up
+ * no operator reaches cudaMalloc/cudaFree. The reference's counterpart is the Arrow memory pool proxy
+ * (ctx/arrow_memory_pool_utils.hpp:24-62). cyl_pool_trim returns every parked block to the driver. */
+int cyl_pool_alloc(void **ptr /* host out */, int64_t bytes, void *stream);
+int cyl_pool_free(void *ptr, void *stream);
+int cyl_pool_trim(void);
 /* Measurement hooks (no counterpart in the reference, which logs std::chrono stage times, e.g. hash_join.cpp:301-304).
  * cyl_launch_count: kernels launched by this library since load. cyl_profile_enable(1) brackets the library's main
  * kernels with CUDA events on their stream; cyl_profile_report synchronises the device and writes
