@@ -12,7 +12,9 @@
 // pass 2 recomputes the partition ids (cheaper than storing 4 B/row) and either emits dest[] or scatters every
 // fixed-width column directly. The scattered stores of one warp form <= P short runs that the 126 MB L2 merges
 // into full lines before they reach HBM.
+#include <memory>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 #include "scan.cuh"
@@ -48,6 +50,14 @@ struct PartArgs {
   int64_t *dest;                      // optional     (PM_DEST)
   unsigned long long *global_hist;    // [P]          (PM_PID_HIST)
   ScatterCols sc;                     // optional fused scatter (PM_DEST)
+  const struct MultiDst *multi;       // optional: one destination set per partition (PM_DEST, with sc.src)
+};
+
+// Per-partition destinations for the scatter that writes straight into other GPUs' receive buffers: partition p's row
+// with stable in-partition rank k lands at dst[c] + (row_base + k) * width. `delta` = row_base - part_offsets[p].
+struct MultiDst {
+  uint8_t *dst[kMaxCols];
+  int64_t delta;
 };
 
 __device__ __forceinline__ uint32_t row_pid(const PartArgs &a, int64_t i) {
@@ -69,6 +79,16 @@ __device__ __forceinline__ void scatter_one(const ScatterCols &sc, int c, int64_
       uint8_t *t = sc.dst[c] + d * (int64_t)w;
       for (int b = 0; b < w; b++) t[b] = s[b];
     }
+  }
+}
+
+__device__ __forceinline__ void scatter_to(uint8_t *dst, int64_t d, const uint8_t *src, int64_t i, int w) {
+  switch (w) {
+    case 8: reinterpret_cast<uint64_t *>(dst)[d] = reinterpret_cast<const uint64_t *>(src)[i]; break;
+    case 4: reinterpret_cast<uint32_t *>(dst)[d] = reinterpret_cast<const uint32_t *>(src)[i]; break;
+    case 16: reinterpret_cast<uint4 *>(dst)[d] = reinterpret_cast<const uint4 *>(src)[i]; break;
+    case 2: reinterpret_cast<uint16_t *>(dst)[d] = reinterpret_cast<const uint16_t *>(src)[i]; break;
+    default: dst[d] = src[i]; break;
   }
 }
 
@@ -137,11 +157,24 @@ __global__ void __launch_bounds__(kPartThreads) partition_tiles_kernel(const __g
             if (d[u] >= 0) a.pid_out[i] = pid[u];
           }
         }
-        for (int c = 0; c < a.sc.n; c++) {
+        if (a.multi) {  // destinations differ per partition (local buffer or a peer GPU's buffer over NVLink)
+          for (int c = 0; c < a.sc.n; c++) {
 #pragma unroll
-          for (int u = 0; u < kUnroll; u++) {
-            const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
-            if (d[u] >= 0) scatter_one(a.sc, c, i, d[u]);
+            for (int u = 0; u < kUnroll; u++) {
+              const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
+              if (d[u] >= 0) {
+                const MultiDst &m = a.multi[pid[u]];
+                scatter_to(m.dst[c], d[u] + m.delta, a.sc.src[c], i, a.sc.width[c]);
+              }
+            }
+          }
+        } else {
+          for (int c = 0; c < a.sc.n; c++) {
+#pragma unroll
+            for (int u = 0; u < kUnroll; u++) {
+              const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
+              if (d[u] >= 0) scatter_one(a.sc, c, i, d[u]);
+            }
           }
         }
       }
@@ -505,5 +538,90 @@ int cyl_partition_scatter_fixed(const cyl_column_t *cols, int32_t ncols, const i
   }
   return partition_map_impl(&k, nullptr, nrows, P, nullptr, nullptr, &sc, part_offsets, (cudaStream_t)stream, "cyl_partition_scatter_fixed");
 }
+
+// ---- two-step form: count first, scatter later into per-partition destinations (fused partition + shuffle) -----------
+struct cyl_partition_plan {
+  PartArgs a;
+  Scratch hist, base, multi;
+  std::vector<int64_t> part_off;  // host copy, [P + 1]
+  int ncols = 0;
+};
+
+int cyl_partition_plan_create(const cyl_column_t *cols, int32_t ncols, const int32_t *key_col_idx, int32_t nkeys, int64_t nrows, uint32_t P,
+                              cyl_partition_plan_t **plan, int64_t *part_rows, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!plan || !part_rows) return fail(CYL_Invalid, "cyl_partition_plan_create: null output");
+  *plan = nullptr;
+  if (ncols < 1 || ncols > kMaxCols) return fail(CYL_Invalid, "cyl_partition_plan_create: %d columns (1..%d)", ncols, kMaxCols);
+  if (nkeys < 1 || nkeys > ncols) return fail(CYL_Invalid, "cyl_partition_plan_create: %d key columns", nkeys);
+  if (P == 0 || P > 1024) return fail(CYL_Invalid, "cyl_partition_plan_create: num_partitions must be in [1, 1024], got %u", P);
+  cyl_column_t kc[kMaxCols];
+  for (int i = 0; i < nkeys; i++) {
+    if (key_col_idx[i] < 0 || key_col_idx[i] >= ncols) return fail(CYL_IndexError, "cyl_partition_plan_create: key column %d out of range", key_col_idx[i]);
+    kc[i] = cols[key_col_idx[i]];
+  }
+  std::unique_ptr<cyl_partition_plan> p(new cyl_partition_plan());
+  PartArgs &a = p->a;
+  memset(&a, 0, sizeof(a));
+  CYL_TRY(make_dcols(kc, nkeys, nrows, &a.keys, "cyl_partition_plan_create"));
+  a.sc.n = ncols;
+  for (int c = 0; c < ncols; c++) {
+    const int w = cols[c].byte_width;
+    if (cols[c].type == CYL_STRING || cols[c].type == CYL_BINARY || !(w == 1 || w == 2 || w == 4 || w == 8 || w == 16))
+      return fail(CYL_Invalid, "cyl_partition_plan_create: column %d is not a 1/2/4/8/16-byte fixed-width column", c);
+    if (cols[c].length != nrows) return fail(CYL_Invalid, "cyl_partition_plan_create: column %d length mismatch", c);
+    a.sc.src[c] = static_cast<const uint8_t *>(cols[c].data);
+    a.sc.width[c] = w;
+  }
+  p->ncols = ncols;
+  a.n = nrows;
+  a.P = P;
+  a.pow2 = (P & (P - 1)) == 0;
+  a.rounds = pick_rounds(nrows, P);
+  a.ntiles = nrows == 0 ? 0 : div_up(nrows, (int64_t)a.rounds * 32);
+  p->part_off.assign(P + 1, 0);
+  if (nrows > 0) {
+    const int64_t ncounters = a.ntiles * P;
+    CYL_TRY(p->hist.alloc((size_t)ncounters * sizeof(uint32_t), s));
+    CYL_TRY(p->base.alloc((size_t)(ncounters + 1) * sizeof(int64_t), s));
+    a.tile_hist = p->hist.as<uint32_t>();
+    {
+      ProfScope ps("partition_tile_hist", s);
+      CYL_TRY(launch_part<PM_TILE_HIST>(a, (size_t)kPartWarps * P * sizeof(uint32_t), s));
+    }
+    CYL_TRY(exclusive_scan<uint32_t>(p->hist.as<uint32_t>(), ncounters, p->base.as<int64_t>(), s));
+    Scratch offs;
+    CYL_TRY(offs.alloc((P + 1) * sizeof(int64_t), s));
+    extract_part_offsets<<<(P + 1 + 255) / 256, 256, 0, s>>>(p->base.as<int64_t>(), a.ntiles, P, offs.as<int64_t>());
+    CYL_LAUNCH_CHECK();
+    CYL_CUDA(cudaMemcpyAsync(p->part_off.data(), offs.p, (P + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+    CYL_CUDA(cudaStreamSynchronize(s));
+    a.tile_base = p->base.as<int64_t>();
+  }
+  for (uint32_t q = 0; q < P; q++) part_rows[q] = p->part_off[q + 1] - p->part_off[q];
+  *plan = p.release();
+  return CYL_OK;
+}
+
+int cyl_partition_plan_scatter(cyl_partition_plan_t *plan, void *const *dst, const int64_t *dst_row_base, void *stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!plan || !dst || !dst_row_base) return fail(CYL_Invalid, "cyl_partition_plan_scatter: null argument");
+  PartArgs a = plan->a;
+  if (a.n == 0) return CYL_OK;
+  std::vector<MultiDst> table(a.P);
+  for (uint32_t p = 0; p < a.P; p++) {
+    memset(&table[p], 0, sizeof(MultiDst));
+    for (int c = 0; c < plan->ncols; c++) table[p].dst[c] = static_cast<uint8_t *>(dst[(size_t)p * plan->ncols + c]);
+    table[p].delta = dst_row_base[p] - plan->part_off[p];
+  }
+  CYL_TRY(plan->multi.alloc(table.size() * sizeof(MultiDst), s));
+  CYL_CUDA(cudaMemcpyAsync(plan->multi.p, table.data(), table.size() * sizeof(MultiDst), cudaMemcpyHostToDevice, s));
+  CYL_CUDA(cudaStreamSynchronize(s));  // `table` is pageable host memory: finish the copy before it goes out of scope
+  a.multi = plan->multi.as<MultiDst>();
+  ProfScope ps("partition_scatter_peer", s);
+  return launch_part<PM_DEST>(a, (size_t)kPartWarps * a.P * sizeof(int64_t), s);
+}
+
+void cyl_partition_plan_free(cyl_partition_plan_t *plan) { delete plan; }
 
 }  // extern "C"

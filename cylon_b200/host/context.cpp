@@ -14,6 +14,7 @@
 #include <nccl.h>
 
 #include <cstdlib>
+#include <map>
 #include <mutex>
 
 #include "../csrc/common.cuh"
@@ -33,6 +34,7 @@ struct NcclApi {
   decltype(&ncclSend) Send = nullptr;
   decltype(&ncclRecv) Recv = nullptr;
   decltype(&ncclAllGather) AllGather = nullptr;
+  decltype(&ncclAllReduce) AllReduce = nullptr;
   decltype(&ncclGetErrorString) GetErrorString = nullptr;
   std::string error;
 };
@@ -61,6 +63,7 @@ NcclApi *LoadNccl() {
     LOAD(Send, "ncclSend")
     LOAD(Recv, "ncclRecv")
     LOAD(AllGather, "ncclAllGather")
+    LOAD(AllReduce, "ncclAllReduce")
     LOAD(GetErrorString, "ncclGetErrorString")
 #undef LOAD
   });
@@ -76,6 +79,61 @@ NcclApi *LoadNccl() {
 class NcclCommunicator : public net::Communicator {
  public:
   NcclCommunicator(NcclApi *api, ncclComm_t comm, int rank, int world) : api_(api), comm_(comm), rank_(rank), world_(world) {}
+
+  Status StreamBarrier(void *stream) override {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!barrier_word_) CUDA_RETURN_IF_FAILED(cudaMalloc(&barrier_word_, 64));
+    NCCL_RETURN_IF_FAILED(api_, api_->AllReduce(barrier_word_, static_cast<char *>(barrier_word_) + 32, 1, ncclInt32, ncclSum, comm_, s));
+    return Status::OK();
+  }
+
+  // Receive buffers of the other ranks, mapped through CUDA IPC so that kernels here can store into them over NVLink.
+  // Handles are cached: the allocator recycles the same blocks step after step, so after warm-up nothing is opened.
+  Status MapPeerBuffers(void *const *mine, int n, void **peers, bool *all_ok, void *stream) override {
+    constexpr int kWords = sizeof(cudaIpcMemHandle_t) / 8;  // 64-byte handle = 8 words
+    std::vector<int64_t> send((size_t)n * kWords), recv((size_t)n * kWords * world_);
+    bool ok = !ipc_broken_;
+    for (int i = 0; i < n && ok; i++) {
+      cudaIpcMemHandle_t h;
+      if (cudaIpcGetMemHandle(&h, mine[i]) != cudaSuccess) {
+        (void)cudaGetLastError();
+        ok = false;
+        break;
+      }
+      memcpy(&send[(size_t)i * kWords], &h, sizeof(h));
+    }
+    RETURN_CYLON_STATUS_IF_FAILED(AllGather(send.data(), n * kWords, recv.data(), stream));
+    for (int r = 0; r < world_ && ok; r++) {
+      for (int i = 0; i < n && ok; i++) {
+        if (r == rank_) {
+          peers[(size_t)r * n + i] = mine[i];
+          continue;
+        }
+        std::string key(reinterpret_cast<const char *>(&recv[((size_t)r * n + i) * kWords]), sizeof(cudaIpcMemHandle_t));
+        auto it = ipc_cache_.find(key);
+        if (it == ipc_cache_.end()) {
+          cudaIpcMemHandle_t h;
+          memcpy(&h, key.data(), sizeof(h));
+          void *p = nullptr;
+          if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            (void)cudaGetLastError();
+            ok = false;
+            break;
+          }
+          it = ipc_cache_.emplace(key, p).first;
+        }
+        peers[(size_t)r * n + i] = it->second;
+      }
+    }
+    // agree: one rank failing means nobody uses peer stores
+    int64_t mine_ok = ok ? 1 : 0;
+    std::vector<int64_t> oks((size_t)world_);
+    RETURN_CYLON_STATUS_IF_FAILED(AllGather(&mine_ok, 1, oks.data(), stream));
+    *all_ok = true;
+    for (int64_t v : oks) *all_ok = *all_ok && v != 0;
+    if (!*all_ok) ipc_broken_ = true;
+    return Status::OK();
+  }
   ~NcclCommunicator() override { Finalize(); }
   int GetRank() const override { return rank_; }
   int GetWorldSize() const override { return world_; }
@@ -88,6 +146,10 @@ class NcclCommunicator : public net::Communicator {
   }
 
   void Finalize() override {
+    for (auto &kv : ipc_cache_) cudaIpcCloseMemHandle(kv.second);
+    ipc_cache_.clear();
+    if (barrier_word_) cudaFree(barrier_word_);
+    barrier_word_ = nullptr;
     if (comm_) {
       api_->CommDestroy(comm_);
       comm_ = nullptr;
@@ -134,6 +196,9 @@ class NcclCommunicator : public net::Communicator {
   NcclApi *api_;
   ncclComm_t comm_;
   int rank_, world_;
+  void *barrier_word_ = nullptr;
+  bool ipc_broken_ = false;
+  std::map<std::string, void *> ipc_cache_;
 };
 
 thread_local std::string g_ctx_error;

@@ -240,6 +240,77 @@ extern "C" int cyl_shuffle_plan(const int64_t *counts, int32_t world, int32_t ra
 
 namespace cylon {
 
+// Fused partition + shuffle over peer memory, for tables whose columns are all fixed width (1/2/4/8/16 bytes) and carry
+// no nulls on any rank: histogram pass -> count exchange -> every rank allocates its output columns and maps the
+// others' through CUDA IPC -> ONE scatter kernel per rank writes each row straight to its final position, locally or
+// in a peer GPU's output column over NVLink. No send buffer, no NCCL payload traffic, no receive-side copy; the two
+// StreamBarriers order the remote stores against the owners' streams. *handled == false: nothing was done and the
+// caller must take the general path (the decision is the same on every rank).
+static Status ShufflePeerScatter(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &table, const std::vector<int> &hash_cols,
+                                 std::shared_ptr<Table> &out, bool *handled) {
+  *handled = false;
+  if (ctx->GetConfig("cylon.shuffle.peer", "1") == "0") return Status::OK();
+  for (const auto &c : table->GetColumns()) {  // schema-only test: identical on every rank
+    const int w = c->byte_width();
+    if (c->is_var_width() || !(w == 1 || w == 2 || w == 4 || w == 8 || w == 16)) return Status::OK();
+  }
+  auto comm = ctx->GetCommunicator();
+  const int P = ctx->GetWorldSize(), rank = ctx->GetRank(), ncols = table->Columns();
+  void *stream = ctx->GetStream();
+  detail::StageTrace trace("shuffle(peer)", stream);
+
+  // the null check needs agreement BEFORE any rank commits to this path
+  std::vector<int64_t> flag(1, 0), flags((size_t)P);
+  for (const auto &c : table->GetColumns()) flag[0] |= c->has_validity() ? 1 : 0;
+  RETURN_CYLON_STATUS_IF_FAILED(comm->AllGather(flag.data(), 1, flags.data(), stream));
+  for (int64_t f : flags)
+    if (f) return Status::OK();
+
+  const auto all = detail::AllDescs(*table);
+  std::vector<int32_t> keys(hash_cols.begin(), hash_cols.end());
+  cyl_partition_plan_t *plan = nullptr;
+  std::vector<int64_t> mine((size_t)P), counts((size_t)P * P);
+  CYL_RETURN_IF_FAILED(cyl_partition_plan_create(all.data(), ncols, keys.data(), (int32_t)keys.size(), table->Rows(), (uint32_t)P, &plan,
+                                                 mine.data(), stream));
+  struct PlanGuard {
+    cyl_partition_plan_t *p;
+    ~PlanGuard() { cyl_partition_plan_free(p); }
+  } guard{plan};
+  trace.mark("histogram");
+  RETURN_CYLON_STATUS_IF_FAILED(comm->AllGather(mine.data(), P, counts.data(), stream));
+  std::vector<int64_t> so(P), sc(P), ro(P), rc(P);
+  int64_t total_rows = 0;
+  CYL_RETURN_IF_FAILED(cyl_shuffle_plan(counts.data(), P, rank, so.data(), sc.data(), ro.data(), rc.data(), &total_rows));
+  if (total_rows > 0xFFFFFFFEll) return Status(Code::CapacityError, "shuffle would put more than 2^32-2 rows on one GPU");
+
+  // my output columns = what the peers write into
+  std::vector<std::shared_ptr<Column>> out_cols((size_t)ncols);
+  std::vector<void *> my_bufs((size_t)ncols), peer_bufs((size_t)ncols * P);
+  for (int c = 0; c < ncols; c++) {
+    const auto &src = table->GetColumn(c);
+    RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(src->name(), src->type(), src->byte_width(), total_rows, total_rows * (int64_t)src->byte_width(),
+                                                   false, stream, &out_cols[c]));
+    my_bufs[c] = out_cols[c]->mutable_data();
+  }
+  bool all_ok = false;
+  RETURN_CYLON_STATUS_IF_FAILED(comm->MapPeerBuffers(my_bufs.data(), ncols, peer_bufs.data(), &all_ok, stream));
+  if (!all_ok) return Status::OK();  // agreed on every rank: general path
+  trace.mark("count exchange + peer mapping");
+
+  // where my rows start in rank g's output: after the rows of lower ranks (chunks ordered by source rank)
+  std::vector<int64_t> dst_base((size_t)P, 0);
+  for (int g = 0; g < P; g++)
+    for (int sr = 0; sr < rank; sr++) dst_base[g] += counts[(size_t)sr * P + g];
+  RETURN_CYLON_STATUS_IF_FAILED(comm->StreamBarrier(stream));  // every owner's stream is past the last use of its buffers
+  CYL_RETURN_IF_FAILED(cyl_partition_plan_scatter(plan, peer_bufs.data(), dst_base.data(), stream));
+  RETURN_CYLON_STATUS_IF_FAILED(comm->StreamBarrier(stream));  // all remote stores have landed before anyone reads
+  trace.mark("scatter to peers");
+  if (!table->IsRetain()) table.reset();
+  out = std::make_shared<Table>(std::move(out_cols), ctx);
+  *handled = true;
+  return Status::OK();
+}
+
 static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &table, const std::vector<int> &hash_cols,
                                std::shared_ptr<Table> &out) {
   auto comm = ctx->GetCommunicator();
@@ -247,6 +318,11 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
   void *stream = ctx->GetStream();
   const int ncols = table->Columns();
 
+  {
+    bool handled = false;
+    RETURN_CYLON_STATUS_IF_FAILED(ShufflePeerScatter(ctx, table, hash_cols, out, &handled));
+    if (handled) return Status::OK();
+  }
   detail::StageTrace trace("shuffle", stream);
   Partitioned pt;
   RETURN_CYLON_STATUS_IF_FAILED(PartitionTable(table, hash_cols, (uint32_t)P, &pt));

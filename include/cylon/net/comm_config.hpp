@@ -59,6 +59,13 @@ class Communicator {
   };
   // one grouped all-to-all over every exchange; the own-rank slice is a device-to-device copy
   virtual Status AllToAllV(const std::vector<Exchange> &exchanges, void *stream) = 0;
+  // cross-GPU ordering point: work enqueued on `stream` after it, on any rank, starts only after every rank's stream
+  // has reached it (and everything those streams did before is complete and visible)
+  virtual Status StreamBarrier(void *stream) = 0;
+  // Peer memory: mine[0..n) are device allocations of this rank (base pointers from the library's allocator). On
+  // success peers[r * n + i] is a pointer THIS GPU can store through to reach rank r's i-th buffer (r == own rank: the
+  // local pointer) and *all_ok tells whether every rank succeeded (ranks must agree before relying on it).
+  virtual Status MapPeerBuffers(void *const *mine, int n, void **peers, bool *all_ok, void *stream) = 0;
 };
 
 }  // namespace net

@@ -114,6 +114,21 @@ int cyl_partition_scatter_fixed(const cyl_column_t *cols /* host array */, int32
                                 int32_t nkeys, int64_t nrows, uint32_t num_partitions, void *const *dst /* host array of device ptrs */,
                                 int64_t *part_offsets, void *stream);
 
+/* Two-step form of the fused partition + scatter, for the shuffle that writes straight into the receivers' buffers:
+ * step 1 counts (tile histograms + scan, kept in the plan) and reports rows per partition on the host (synchronises);
+ * the caller exchanges the counts, learns where each partition has to go, and step 2 scatters partition p's rows, in
+ * stable order, to dst[p * ncols + c] + (dst_row_base[p] + k) * width for the k-th row of the partition. The
+ * destination pointers may be device memory of ANOTHER GPU mapped into this process (cudaIpcOpenMemHandle): the
+ * stores then travel over NVLink and no send buffer or separate copy exists. All columns fixed width (1/2/4/8/16).
+ * Replaces Split + ArrowAllToAll's per-buffer sends (partition/partition.cpp:27-90, arrow/arrow_all_to_all.cpp:68-151). */
+typedef struct cyl_partition_plan cyl_partition_plan_t;
+int cyl_partition_plan_create(const cyl_column_t *cols /* host array */, int32_t ncols, const int32_t *key_col_idx /* host */, int32_t nkeys,
+                              int64_t nrows, uint32_t num_partitions, cyl_partition_plan_t **plan /* host out */,
+                              int64_t *part_rows /* host out [P] */, void *stream);
+int cyl_partition_plan_scatter(cyl_partition_plan_t *plan, void *const *dst /* host array [P * ncols] of device pointers */,
+                               const int64_t *dst_row_base /* host [P] */, void *stream);
+void cyl_partition_plan_free(cyl_partition_plan_t *plan);
+
 /* ---------------------------------------------------------------- scan ------------------------- */
 /* out[i] = sum_{j<i} in[j]; out has n+1 entries (out[n] = total). In place (out == in) is NOT allowed. */
 int cyl_exclusive_scan_i64(const int64_t *in, int64_t n, int64_t *out, void *stream);
