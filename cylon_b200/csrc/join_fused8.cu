@@ -402,9 +402,11 @@ static int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n,
                         cudaStream_t s) {
   // Measured on B200 at 100M rows x 32768 bins (profiles/r01_fused_join_notes.md): block-private cursors make the
   // scatter SLOWER (4.4 ms vs 2.9 ms) because 148 CTAs x 32768 bins leave ~5M partially written lines in flight, far
-  // more than L2 can hold until they fill; shared global cursors keep only K write frontiers alive. So: block-private
-  // ranges only while a (tile, bin) run is long enough to fill lines, else shared cursors -- but always the
-  // shared-memory histogram, which is 4x faster than global reductions.
+  // more than L2 can hold until they fill; shared global cursors keep only K write frontiers alive. A two-level split
+  // (2048 coarse bins with block-private cursors, then one CTA per coarse bin) was also measured and rejected: its first
+  // level alone took 2.8 ms (shared-memory atomic and store-queue stalls), 4.3 ms per table in total against 3.1 ms.
+  // So: block-private ranges only while a (tile, bin) run is long enough to fill lines, else shared cursors -- but
+  // always the shared-memory histogram, which is 4x faster than global reductions.
   const int64_t tile_guess = n / ((int64_t)num_sms() * 4) + 1;
   if (nbins <= kBlkMaxBins && tile_guess / nbins >= 32) return f8_partition_blocks(cols, ncols, key, n, nbins, shift, rec, bin_off, s);
   F8PartArgs a;

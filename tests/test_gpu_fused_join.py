@@ -116,3 +116,28 @@ def test_table_join_takes_fused_path_and_matches_general_path():
     assert fused.row_count == m_ref and fused.checksum() == cs_ref
     assert fused.column_names == ["l_k", "l_v", "r_k", "r_v"]
     ctx.finalize()
+
+
+@pytest.mark.parametrize("skew", [False, True])
+def test_fused_join_large(skew):
+    """7M x 7M rows (32768 bins, shared-memory histogram + global cursors; with `skew` one bin is far above the
+    shared-memory capacity and is probed in build chunks): result checked against the oracle by row count +
+    order-independent checksum, and against the GPU sort join (independent code path)."""
+    from cylon_b200 import api
+    ctx = api.CylonContext(device=0)
+    n = 7_000_000
+    lk, lv = synth_kv(n, n, 21)
+    rk, rv = synth_kv(n, n, 22)
+    if skew:
+        lk[: n // 3] = 12345  # one hot key on the build side: a coarse bin far above the average, and build chunks in the probe
+        rk[:50] = 12345
+    l = [orc.col(lk, name="k"), orc.col(lv, name="v")]
+    r = [orc.col(rk, name="k"), orc.col(rv, name="v")]
+    L, R = from_orc(api, ctx, l), from_orc(api, ctx, r)
+    fused = L.join(R, "inner", "hash", [0], [0])
+    m_ref, cs_ref = orc.join_i64_f64(lk, lv, rk, rv, orc.INNER, orc.HASH)
+    assert fused.row_count == m_ref
+    assert fused.checksum() == cs_ref
+    general = L.join(R, "inner", "sort", [0], [0])
+    assert general.row_count == m_ref and general.checksum() == cs_ref
+    ctx.finalize()
