@@ -255,11 +255,11 @@ def main():
         state["rows"] = out.row_count
         out.free()
 
+    sampler = ClockSampler(local_rank)  # samples through warm-up, the timed steps and the e2e steps (all under load)
+    sampler.start()
     for _ in range(args.warmup):
         step()
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     launches0 = capi.launch_count()
     capi.profile_enable(True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -268,7 +268,6 @@ def main():
         step()
     ev1.record()
     barrier()
-    sampler.stop_flag.set()
     launches = capi.launch_count() - launches0
     capi.profile_enable(False)
     prof = capi.profile_report()
@@ -315,6 +314,7 @@ def main():
         e2e = {"value": 2.0 * rows * world / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(2 * rows * 16),
                "d2h_bytes_per_step": int(mm * 32), "ms_per_step": e2e_ms}
 
+    sampler.stop_flag.set()
     if rank != 0:
         ctx.finalize()
         return 0
@@ -337,8 +337,18 @@ def main():
         per_launch_ms = dom_ms / max(1, dom_n)
         ab = algorithmic_bytes(dominant, rows, m)
         achieved = ab / 1e9 / (per_launch_ms / 1e3)
+        # dram__bytes_read+write per launch from the committed `ncu --set full` capture (only valid for the size it was taken at)
+        traffic = None
+        scope_to_kernel = {"fused_join_scatter": "void fused8_scatter_kernel<2>", "fused_join_probe": "void fused8_join_kernel<2, 2>",
+                           "fused_join_hist": "fused8_block_hist_kernel"}
+        try:
+            if rows == 100_000_000:
+                with open(os.path.join(ROOT, "profiles", "r01_traffic_100M.json")) as f:
+                    traffic = json.load(f).get(scope_to_kernel.get(dominant, ""))
+        except Exception:
+            traffic = None
         roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab, "ms_per_launch": per_launch_ms}
+                    "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab, "ms_per_launch": per_launch_ms}
     # whole local join against its algorithmic bytes ((N_L+N_R)*w + M*(w_L+w_R))
     step_bytes = 2 * rows * 16 + m * 32
     step_roofline = {"algorithmic_bytes": step_bytes, "achieved_GBps": step_bytes / 1e9 / (ms_per_step / 1e3),
