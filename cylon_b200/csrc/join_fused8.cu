@@ -117,8 +117,9 @@ template <int BW, int PW>
 __global__ void __launch_bounds__(kF8Threads) fused8_join_kernel(const __grid_constant__ F8JoinArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ unsigned int s_bin;
-  __shared__ unsigned int s_warp_tot[kF8Threads / 32];
+  __shared__ unsigned int s_warp_tot[kF8ProbeRows][kF8Threads / 32];
   __shared__ unsigned long long s_base;
+  __shared__ unsigned int s_total;
   uint64_t *brec = reinterpret_cast<uint64_t *>(smem);                                  // [cap_rows][BW]
   uint32_t *heads = reinterpret_cast<uint32_t *>(smem + (size_t)a.cap_rows * BW * 8);   // [nheads]
   uint16_t *next = reinterpret_cast<uint16_t *>(heads + a.nheads);                      // [cap_rows]
@@ -195,36 +196,60 @@ __global__ void __launch_bounds__(kF8Threads) fused8_join_kernel(const __grid_co
           }
           mine += cnt[u];
         }
-        unsigned int inc = mine;
+        // Output slots are handed out u-major (every thread's probe row 0, then every thread's row 1, ...): inside one
+        // store instruction the lanes then write consecutive output rows, i.e. whole sectors. (Thread-major slots cost
+        // 3.6 L2 sector writes per sector of output: ncu, profiles/r01_ncu_final.md.)
+        unsigned int inc[kF8ProbeRows];
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const unsigned int n = __shfl_up_sync(0xffffffffu, inc, d);
-          if (lane >= d) inc += n;
-        }
-        if (lane == 31) s_warp_tot[warp] = inc;
-        __syncthreads();
-        unsigned int wbase = 0, total = 0;
+        for (int u = 0; u < kF8ProbeRows; u++) {
+          inc[u] = cnt[u];
 #pragma unroll
-        for (int w = 0; w < kF8Threads / 32; w++) {
-          const unsigned int t = s_warp_tot[w];
-          if (w < warp) wbase += t;
-          total += t;
+          for (int d = 1; d < 32; d <<= 1) {
+            const unsigned int n = __shfl_up_sync(0xffffffffu, inc[u], d);
+            if (lane >= d) inc[u] += n;
+          }
+          if (lane == 31) s_warp_tot[u][warp] = inc[u];
         }
-        if (tid == 0 && total) s_base = atomicAdd(a.out_cursor, (unsigned long long)total);
         __syncthreads();
+        if (warp == 0) {  // one warp turns the per-warp totals into exclusive bases (u-major) for everybody
+          unsigned int run = 0;
+#pragma unroll
+          for (int u = 0; u < kF8ProbeRows; u++) {
+            const unsigned int t = lane < kF8Threads / 32 ? s_warp_tot[u][lane] : 0u;
+            unsigned int sc = t;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+              const unsigned int n = __shfl_up_sync(0xffffffffu, sc, d);
+              if (lane >= d) sc += n;
+            }
+            if (lane < kF8Threads / 32) s_warp_tot[u][lane] = run + sc - t;
+            run += __shfl_sync(0xffffffffu, sc, 31);
+          }
+          if (lane == 0) {
+            s_total = run;
+            if (run) s_base = atomicAdd(a.out_cursor, (unsigned long long)run);  // one reservation per tile
+          }
+        }
+        __syncthreads();
+        const unsigned int total = s_total;
+        unsigned int slot0[kF8ProbeRows];
+#pragma unroll
+        for (int u = 0; u < kF8ProbeRows; u++) slot0[u] = s_warp_tot[u][warp] + inc[u] - cnt[u];
         if (mine && (int64_t)s_base + total <= a.capacity) {
-          int64_t o = (int64_t)s_base + wbase + inc - mine;
 #pragma unroll
           for (int u = 0; u < kF8ProbeRows; u++) {
             if (cnt[u] == 0) continue;
+            int64_t o = (int64_t)s_base + slot0[u];
+            unsigned int left = cnt[u];
             const uint64_t k = f8_canon(f8_pick<PW>(pv[u], a.pkey), a.key_is_f64);
-            for (uint32_t j = first[u]; j != kF8Nil; j = next[j]) {
+            for (uint32_t j = first[u]; left; j = next[j]) {
               if (j != first[u] && f8_canon(brec[j * BW + a.bkey], a.key_is_f64) != k) continue;
 #pragma unroll
               for (int w = 0; w < BW; w++) a.bout[w][o] = brec[j * BW + w];
 #pragma unroll
               for (int w = 0; w < PW; w++) a.pout[w][o] = pv[u][w];
               o++;
+              left--;
             }
           }
         }
