@@ -117,6 +117,7 @@ def algorithmic_bytes(kernel, n, m):
         "fused_join_offsets": 0,
         "fused_join_scatter": n * 16 * 2,    # per launch (one table): (key, payload) columns in + packed records out
         "fused_join_probe": 2 * n * 16 + m * 32,  # both record streams in + the 4 result columns out (= SURVEY 8d local join)
+        "partition_scatter_peer": n * 16 * 2,  # per launch (one table): rows in + rows out (remote share over NVLink)
         "partition_tile_hist": n * 8,
         "partition_scatter": n * 16 * 2,     # whole (key, payload) table in + out
         "partition_scan": 0,

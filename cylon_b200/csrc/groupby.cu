@@ -158,6 +158,7 @@ static int aggregate_typed(const void *data, const int64_t *gid, int64_t n, int6
     CYL_LAUNCH_CHECK();
   }
   if (n > 0) {
+    ProfScope ps("groupby_aggregate", s);
     aggregate_kernel<T, OP><<<grid1d(n), 256, 0, s>>>(static_cast<const T *>(data), gid, n, acc);
     CYL_LAUNCH_CHECK();
   }
@@ -210,7 +211,10 @@ int cyl_groupby_hash(const cyl_column_t *keys, int32_t nkeys, int64_t nrows, int
   for (int attempt = 0;; attempt++) {
     if (attempt > 64) return fail(CYL_ExecutionError, "cyl_groupby_hash: could not place all keys");
     CYL_TRY(rt.alloc(cap, s));
-    CYL_TRY(rowtable_insert(rt, a.keys, nrows, a.exact != 0, seed, 0, pslot.as<uint32_t>()));
+    {
+      ProfScope ps("groupby_insert", s);
+      CYL_TRY(rowtable_insert(rt, a.keys, nrows, a.exact != 0, seed, 0, pslot.as<uint32_t>()));
+    }
     int overflow = 0, collision = 0;
     CYL_TRY(rt.read_flags(&overflow, &collision));
     if (overflow) {
@@ -219,8 +223,11 @@ int cyl_groupby_hash(const cyl_column_t *keys, int32_t nkeys, int64_t nrows, int
       continue;
     }
     a.t = rt.t;
-    group_flag_kernel<<<grid1d(nrows), 256, 0, s>>>(a);
-    CYL_LAUNCH_CHECK();
+    {
+      ProfScope ps("groupby_flag", s);
+      group_flag_kernel<<<grid1d(nrows), 256, 0, s>>>(a);
+      CYL_LAUNCH_CHECK();
+    }
     if (!a.exact) {
       CYL_TRY(rt.read_flags(&overflow, &collision));
       if (collision) {  // two unequal key tuples share a 64-bit tag: redo with another seed
@@ -230,12 +237,18 @@ int cyl_groupby_hash(const cyl_column_t *keys, int32_t nkeys, int64_t nrows, int
     }
     break;
   }
-  CYL_TRY(exclusive_scan<uint8_t>(first_mask, nrows, pos.as<int64_t>(), s));
+  {
+    ProfScope ps("groupby_scan", s);
+    CYL_TRY(exclusive_scan<uint8_t>(first_mask, nrows, pos.as<int64_t>(), s));
+  }
   a.pos = pos.as<int64_t>();
-  group_publish_kernel<<<grid1d(nrows), 256, 0, s>>>(a);
-  CYL_LAUNCH_CHECK();
-  group_assign_kernel<<<grid1d(nrows), 256, 0, s>>>(a);
-  CYL_LAUNCH_CHECK();
+  {
+    ProfScope ps("groupby_assign_ids", s);
+    group_publish_kernel<<<grid1d(nrows), 256, 0, s>>>(a);
+    CYL_LAUNCH_CHECK();
+    group_assign_kernel<<<grid1d(nrows), 256, 0, s>>>(a);
+    CYL_LAUNCH_CHECK();
+  }
   int64_t g = 0;
   CYL_CUDA(cudaMemcpyAsync(&g, pos.as<int64_t>() + nrows, sizeof(int64_t), cudaMemcpyDeviceToHost, s));
   CYL_CUDA(cudaStreamSynchronize(s));
@@ -251,6 +264,7 @@ int cyl_aggregate(const cyl_column_t *col, const int64_t *gid, int64_t num_group
   if (op == CYL_AGG_COUNT) {  // CountKernel: counts every row, nulls included (aggregate_kernels.hpp:432-447)
     CYL_CUDA(cudaMemsetAsync(out, 0, (size_t)(num_groups ? num_groups : 1) * sizeof(int64_t), s));
     if (n > 0) {
+      ProfScope ps("groupby_aggregate", s);
       count_kernel<<<grid1d(n), 256, 0, s>>>(gid, n, static_cast<unsigned long long *>(out));
       CYL_LAUNCH_CHECK();
     }

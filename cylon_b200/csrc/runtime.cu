@@ -218,10 +218,7 @@ const char *cyl_last_error(void) { return g_err; }
 
 int cyl_init(int32_t device) {
   CYL_CUDA(cudaSetDevice(device));
-  cudaMemPool_t pool;
-  CYL_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
-  uint64_t threshold = UINT64_MAX;  // keep freed scratch in the pool: no cudaMalloc/cudaFree on the hot path
-  CYL_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+  CYL_CUDA(cudaFree(nullptr));  // create the context now, not inside the first operator
   return CYL_OK;
 }
 

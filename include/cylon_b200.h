@@ -9,8 +9,8 @@
  *     asynchronous on that stream unless they return a host value (documented per call).
  *   - every call returns a cylon::Code (cyl_code_t; 0 = OK), the convention of cpp/src/cylon/status.hpp:21-63.
  *     cyl_last_error() gives the message of the calling thread's last failure.
- *   - scratch memory is taken from the device's stream-ordered pool (cudaMallocAsync) and returned before
- *     the call ends (stream-ordered).
+ *   - scratch memory comes from the library's caching allocator (cyl_pool_*) and is handed back before the call
+ *     returns; it is reused only by later work on the same stream.
  *   - citations are relative to /root/reference/cpp/src/cylon/ and name the reference code each entry
  *     point replaces.
  */
@@ -26,7 +26,7 @@ extern "C" {
 /* ---------------------------------------------------------------- runtime ---------------------- */
 int cyl_version(void);
 const char *cyl_last_error(void); /* host string, valid until the thread's next failing call */
-/* Selects `device` for the calling thread and lets the default memory pool keep freed blocks.
+/* Selects `device` for the calling thread and creates its CUDA context.
  * (The reference's counterpart is CylonContext::Init, ctx/cylon_context.cpp:24-30 -- host only.) */
 int cyl_init(int32_t device);
 int cyl_device_count(int32_t *count /* host */);

@@ -30,10 +30,22 @@ def timed(label, fn, **extra):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--only", default="", help="comma list of configs to run: 3,4,5")
     args = ap.parse_args()
     ctx = api.CylonContext(device=0)
     rng = np.random.default_rng(1)
 
+    only = set(args.only.split(",")) if args.only else {"3", "4", "5"}
+    if "3" in only:
+        config3(ctx, rng, args)
+    if "4" in only:
+        config4(ctx, rng, args)
+    if "5" in only:
+        config5(ctx, rng, args)
+    ctx.finalize()
+
+
+def config3(ctx, rng, args):
     # ---------------- config 3: left/right/full-outer SortJoin, key (int64, int32), Zipf(1.1) left side
     n = int(50_000_000 * args.scale)
     rk0 = np.arange(n, dtype=np.int64)
@@ -55,6 +67,9 @@ def main():
     left.free()
     right.free()
 
+
+
+def config4(ctx, rng, args):
     # ---------------- config 4: hash GroupBy sum/count/min/max, 125M rows, 1M groups
     n = int(125_000_000 * args.scale)
     groups = 1_000_000
@@ -62,7 +77,10 @@ def main():
     v = np.maximum(rng.random(n), np.finfo(np.float64).tiny)
     t = api.Table.from_numpy(ctx, [g, v], names=["g", "v"])
     for rep in range(2):
+        capi.profile_enable(rep == 1)
         out, rec = timed("hash_groupby_sum_count_min_max", lambda: t.groupby(0, [1, 1, 1, 1], ["sum", "count", "min", "max"]), rows=n)
+    capi.profile_enable(False)
+    rec["kernels_ms"] = {k: round(v[1], 3) for k, v in capi.profile_report().items()}
     host = out.to_host()
     ok = (out.row_count == len(np.unique(g)) and int(host[2]["data"].sum()) == n
           and abs(float(host[1]["data"].sum()) - float(v.sum())) <= 1e-9 * float(v.sum())
@@ -73,6 +91,9 @@ def main():
     out.free()
     t.free()
 
+
+
+def config5(ctx, rng, args):
     # ---------------- config 5a: union / intersect / subtract / unique, 25M rows, (int64, string, double) rows
     n = int(25_000_000 * args.scale)
     words = np.array([("w%07d" % i)[: 4 + i % 21].encode() for i in range(1_000_000)], dtype=object)
@@ -100,7 +121,6 @@ def main():
         out, rec = timed("unique_cols_0_1", lambda: A.unique([0, 1]), rows=n)
     rec.update(out_rows=out.row_count, expected_rows=da, ok=(out.row_count == da), rows_per_s=round(n / (rec["ms"] / 1e3)))
     print(json.dumps(rec), flush=True)
-    ctx.finalize()
 
 
 if __name__ == "__main__":
