@@ -279,7 +279,20 @@ __global__ void __launch_bounds__(kPartThreads) partition_stage_scatter_kernel(c
       const int64_t gbase = a.tile_base[(int64_t)p * a.ntiles + tile] + m.delta;
       for (int c = 0; c < a.sc.n; c++) {
         const unsigned char *col = stage + (size_t)s.col_off[c];
-        for (uint32_t k = lane; k < cnt; k += 32) scatter_to(m.dst[c], gbase + k, col, first + k, a.sc.width[c]);
+        if (a.sc.width[c] == 8) {  // 8-byte columns: 128-bit stores (512 B per warp instruction) once the destination is 16-byte aligned
+          const uint64_t *src64 = reinterpret_cast<const uint64_t *>(col) + first;
+          uint64_t *dst64 = reinterpret_cast<uint64_t *>(m.dst[c]) + gbase;
+          const uint32_t head = (uint32_t)(gbase & 1);  // element offsets are 8 bytes: odd gbase = misaligned by 8
+          if (head && lane == 0) dst64[0] = src64[0];
+          const uint32_t npairs = (cnt - head) >> 1;
+          for (uint32_t q = lane; q < npairs; q += 32) {
+            const uint32_t k = head + 2 * q;
+            *reinterpret_cast<ulonglong2 *>(dst64 + k) = make_ulonglong2(src64[k], src64[k + 1]);
+          }
+          if (((cnt - head) & 1) && lane == 0) dst64[cnt - 1] = src64[cnt - 1];
+        } else {
+          for (uint32_t k = lane; k < cnt; k += 32) scatter_to(m.dst[c], gbase + k, col, first + k, a.sc.width[c]);
+        }
       }
     }
     __syncwarp();
