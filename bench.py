@@ -367,8 +367,10 @@ def main():
         line["e2e"] = e2e
     if not args.no_cpu and world == 1:
         line["cpu_baseline"] = cpu_baseline(np.asarray(lk), np.asarray(lv), np.asarray(rk), np.asarray(rv), min(args.cpu_rows, rows))
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     ctx.finalize()
+    if world > 1:
+        dist.destroy_process_group()
     return 0
 
 

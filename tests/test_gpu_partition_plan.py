@@ -82,3 +82,31 @@ def test_plan_scatter_mixed_widths_and_wide_rows(cy, P):
             idx = perm[offs[p]:offs[p + 1]]
             for got, c in zip(parts[p], ocols):
                 assert np.array_equal(got, c.data[idx])
+
+
+@pytest.mark.parametrize("P", [2, 3, 5, 8, 16])
+@pytest.mark.parametrize("layout", ["k", "kv", "vk", "kvv", "vkv", "vvk", "dk_v", "two_keys"])
+def test_plan_scatter_all_8_byte_variants(cy, P, layout):
+    """Every instantiation of the all-8-byte staged kernel (1-3 columns x key position, int64 'modulo' key, double
+    'murmur' key, two-column key = generic row hash), on row bases of
+    both parities and ragged tails."""
+    rng = np.random.default_rng(P * 31 + len(layout))
+    n = 100_003
+    ik = lambda: orc.col(rng.integers(-2 ** 40, 2 ** 40, n).astype(np.int64))  # noqa: E731
+    dv = lambda: orc.col(rng.random(n))  # noqa: E731
+    if layout == "dk_v":
+        ocols, keys = [orc.col(rng.integers(0, 5000, n).astype(np.float64)), ik()], [0]
+    elif layout == "two_keys":
+        ocols, keys = [ik(), ik(), dv()], [0, 1]
+    else:
+        ocols = [ik() if ch == "k" else dv() for ch in layout]
+        keys = [layout.index("k")]
+    for shift in (0, 1):
+        rows, parts = _run(cy, ocols, keys, P, row_base_shift=shift)
+        pid, hist = orc.hash_partition([ocols[k] for k in keys], P)
+        perm, offs = orc.split_indices(pid, P)
+        assert rows == [int(h) for h in hist]
+        for p in range(P):
+            idx = perm[offs[p]:offs[p + 1]]
+            for got, c in zip(parts[p], ocols):
+                assert np.array_equal(got, c.data[idx])
