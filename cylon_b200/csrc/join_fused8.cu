@@ -423,6 +423,345 @@ static int f8_partition_blocks(const cyl_column_t *cols, int ncols, int key, int
   return CYL_OK;
 }
 
+// ---- two-pass staged radix partitioner -----------------------------------------------------------------------------
+// What limits every single-pass variant above is one scattered 16-byte store per row (~35 G/s chip-wide). Splitting the
+// bin number into a coarse digit (<= 8 bits) and a fine digit (<= 8 bits) lets a CTA sort a 4096-row tile by ONE digit
+// inside shared memory and write each (tile, digit) run as consecutive records: 16-32 rows, 256-512 contiguous bytes, so
+// the stores coalesce and the pass runs near copy speed. Two such passes move 4x the table's bytes and still beat one
+// pass of scattered stores. Slots inside a run come from shared-memory atomics, ranges inside a bin from one global
+// atomicAdd per (tile, digit) on cursors preset from the full K-bin histogram -- row order inside a bin is arbitrary,
+// as it already was. All of a tile's loads are issued before the first use.
+constexpr int kRsThreads = 256;
+static int64_t g_two_pass_min_rows = 1 << 21;  // below this the launch count matters more than the store pattern
+constexpr int kRsMaxDigits = 256;
+
+struct F8RadixArgs {
+  const uint64_t *cols[kFused8MaxCols];  // pass A input (columns)
+  const uint64_t *src;                   // pass B input (records ordered by coarse digit)
+  uint64_t *dst;
+  int32_t key, key_is_f64, shift, lo_bits, ndigits, cols_aligned16;
+  int64_t n;
+  unsigned int *cursor;                  // pass A: [coarse]; pass B: [K]
+  const int64_t *bin_off;                // [K + 1]
+  const unsigned int *tile_prefix;       // pass B: [ncoarse + 1] tiles before each coarse partition
+  int32_t ncoarse;
+};
+
+template <int W>
+struct RsCfg {
+  static constexpr int R = W <= 2 ? 16 : 8;  // rows per thread
+  static constexpr int T = R * kRsThreads;   // rows per tile: 64 KB of records for W = 2 and W = 4
+};
+
+__global__ void fused8_tile_prefix_kernel(const int64_t *__restrict__ bin_off, int lo_bits, int ncoarse, int tile_rows, unsigned int *__restrict__ prefix) {
+  __shared__ unsigned int s[kRsMaxDigits + 1];
+  const int h = threadIdx.x;
+  if (h < ncoarse) {
+    const int64_t rows = bin_off[(int64_t)(h + 1) << lo_bits] - bin_off[(int64_t)h << lo_bits];
+    s[h + 1] = (unsigned int)((rows + tile_rows - 1) / tile_rows);
+  }
+  if (h == 0) s[0] = 0;
+  __syncthreads();
+  if (h == 0)
+    for (int i = 1; i <= ncoarse; i++) s[i] += s[i - 1];
+  __syncthreads();
+  if (h <= ncoarse) prefix[h] = s[h];
+}
+
+__global__ void fused8_coarse_cursor_kernel(const int64_t *__restrict__ bin_off, int lo_bits, int ncoarse, unsigned int *__restrict__ cursor) {
+  const int h = blockIdx.x * blockDim.x + threadIdx.x;
+  if (h < ncoarse) cursor[h] = (unsigned int)bin_off[(int64_t)h << lo_bits];
+}
+
+template <int W, bool PASS_B>
+__global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const __grid_constant__ F8RadixArgs a) {
+  constexpr int R = RsCfg<W>::R;
+  constexpr int T = RsCfg<W>::T;
+  extern __shared__ __align__(16) unsigned char rs_smem[];
+  uint64_t *stage = reinterpret_cast<uint64_t *>(rs_smem);                     // [T][W]
+  unsigned int *cnt = reinterpret_cast<unsigned int *>(stage + (size_t)T * W);  // [256] rows per digit, then run starts
+  unsigned int *delta = cnt + kRsMaxDigits;                                     // [256] destination - staging slot
+  unsigned int *warp_tot = delta + kRsMaxDigits;                                // [8]
+  unsigned int *prefix = warp_tot + 8;                                          // [257] (pass B)
+  uint8_t *slot_digit = reinterpret_cast<uint8_t *>(prefix + kRsMaxDigits + 1); // [T]
+  const int tid = threadIdx.x;
+  const unsigned lane = tid & 31, warp = tid >> 5;
+  const uint32_t lo_mask = (1u << a.lo_bits) - 1;
+
+  int64_t ntiles;
+  if (PASS_B) {
+    for (int i = tid; i <= a.ncoarse; i += kRsThreads) prefix[i] = a.tile_prefix[i];
+    __syncthreads();
+    ntiles = prefix[a.ncoarse];
+  } else {
+    ntiles = (a.n + T - 1) / T;
+  }
+  // rows [r0, r1) of tile g and (pass B) the first fine cursor of its coarse partition
+  auto tile_range = [&](int64_t g, int64_t &r0, int64_t &r1, uint32_t &cursor_base) {
+    cursor_base = 0;
+    if (PASS_B) {
+      int lo = 0, hi = a.ncoarse;  // last h with prefix[h] <= g
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (prefix[mid] <= (unsigned int)g) lo = mid; else hi = mid;
+      }
+      const int64_t p0 = a.bin_off[(int64_t)lo << a.lo_bits], p1 = a.bin_off[(int64_t)(lo + 1) << a.lo_bits];
+      r0 = p0 + (g - prefix[lo]) * T;
+      r1 = r0 + T < p1 ? r0 + T : p1;
+      cursor_base = (uint32_t)lo << a.lo_bits;
+    } else {
+      r0 = g * T;
+      r1 = r0 + T < a.n ? r0 + T : a.n;
+    }
+  };
+  // Thread `tid` owns rows r0 + (u/2)*2*256 + 2*tid + (u&1): pairs of neighbouring rows, so that column input can be read
+  // with 128-bit loads when the tile start is 16-byte aligned (r0 is even and the column base is).
+  uint64_t v[R][W];
+  auto row_of = [&](int64_t r0, int u) { return r0 + (int64_t)(u >> 1) * (2 * kRsThreads) + 2 * tid + (u & 1); };
+  auto load_tile = [&](int64_t r0, int64_t r1) {
+    if (PASS_B) {
+#pragma unroll
+      for (int u = 0; u < R; u++) {
+        const int64_t i = row_of(r0, u);
+        if constexpr (W == 2) {
+          ulonglong2 t = make_ulonglong2(0, 0);
+          if (i < r1) t = __ldcs(reinterpret_cast<const ulonglong2 *>(a.src + i * 2));
+          v[u][0] = t.x;
+          v[u][1] = t.y;
+        } else if constexpr (W == 4) {
+          ulonglong2 t0 = make_ulonglong2(0, 0), t1 = t0;
+          if (i < r1) {
+            t0 = __ldcs(reinterpret_cast<const ulonglong2 *>(a.src + i * 4));
+            t1 = __ldcs(reinterpret_cast<const ulonglong2 *>(a.src + i * 4 + 2));
+          }
+          v[u][0] = t0.x; v[u][1] = t0.y; v[u][2] = t1.x; v[u][3] = t1.y;
+        } else {
+#pragma unroll
+          for (int w = 0; w < W; w++) v[u][w] = i < r1 ? ld_stream_u64(a.src + i * W + w) : 0;
+        }
+      }
+    } else if (a.cols_aligned16 && !(r0 & 1)) {
+#pragma unroll
+      for (int u = 0; u < R; u += 2) {
+        const int64_t i = row_of(r0, u);
+#pragma unroll
+        for (int w = 0; w < W; w++) {
+          ulonglong2 t = make_ulonglong2(0, 0);
+          if (i + 1 < r1) t = __ldcs(reinterpret_cast<const ulonglong2 *>(a.cols[w] + i));
+          else if (i < r1) t.x = ld_stream_u64(a.cols[w] + i);
+          v[u][w] = t.x;
+          v[u + 1][w] = t.y;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < R; u++) {
+        const int64_t i = row_of(r0, u);
+#pragma unroll
+        for (int w = 0; w < W; w++) v[u][w] = i < r1 ? ld_stream_u64(a.cols[w] + i) : 0;
+      }
+    }
+  };
+
+  int64_t r0 = 0, r1 = 0;
+  uint32_t cursor_base = 0;
+  if ((int64_t)blockIdx.x < ntiles) {
+    tile_range(blockIdx.x, r0, r1, cursor_base);
+    load_tile(r0, r1);
+  }
+  for (int64_t g = blockIdx.x; g < ntiles; g += gridDim.x) {
+    cnt[tid] = 0;
+    __syncthreads();  // counters are zero
+    uint32_t dr[R];   // digit << 16 | rank inside the (tile, digit) run
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      const int64_t i = row_of(r0, u);
+      const uint32_t bin = f8_bin(f8_canon(f8_pick<W>(v[u], a.key), a.key_is_f64), a.shift);
+      const uint32_t d = PASS_B ? (bin & lo_mask) : (bin >> a.lo_bits);
+      dr[u] = i < r1 ? ((d << 16) | atomicAdd(&cnt[d], 1u)) : 0xFFFFFFFFu;
+    }
+    __syncthreads();
+    {  // exclusive scan of the 256 counters; digit `tid` reserves its run's destination range
+      const unsigned int c = cnt[tid];
+      unsigned int inc = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= (unsigned)d) inc += t;
+      }
+      if (lane == 31) warp_tot[warp] = inc;
+      unsigned int g0 = 0;
+      if (c) g0 = atomicAdd(&a.cursor[cursor_base + tid], c);
+      __syncthreads();
+      unsigned int before = 0;
+#pragma unroll
+      for (int w = 0; w < kRsThreads / 32; w++) before += w < (int)warp ? warp_tot[w] : 0u;
+      const unsigned int start = before + inc - c;
+      cnt[tid] = start;
+      delta[tid] = g0 - start;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < R; u++) {
+      if (dr[u] != 0xFFFFFFFFu) {
+        const uint32_t d = dr[u] >> 16, slot = cnt[d] + (dr[u] & 0xFFFFu);
+        if constexpr (W == 2) {
+          *reinterpret_cast<ulonglong2 *>(stage + (size_t)slot * 2) = make_ulonglong2(v[u][0], v[u][1]);
+        } else {
+#pragma unroll
+          for (int w = 0; w < W; w++) stage[(size_t)slot * W + w] = v[u][w];
+        }
+        slot_digit[slot] = (uint8_t)d;
+      }
+    }
+    const int nvalid = (int)(r1 - r0);
+    if (g + gridDim.x < ntiles) {  // the registers are free again: the next tile's loads fly while this one is written out
+      tile_range(g + gridDim.x, r0, r1, cursor_base);
+      load_tile(r0, r1);
+    }
+    __syncthreads();
+    for (int j = tid; j < nvalid; j += kRsThreads) {  // consecutive threads -> consecutive records of a run
+      const uint32_t d = slot_digit[j];
+      const uint32_t pos = delta[d] + (uint32_t)j;
+      uint64_t rec[W];
+      if constexpr (W == 2) {
+        const ulonglong2 t = *reinterpret_cast<const ulonglong2 *>(stage + (size_t)j * 2);
+        rec[0] = t.x;
+        rec[1] = t.y;
+      } else {
+#pragma unroll
+        for (int w = 0; w < W; w++) rec[w] = stage[(size_t)j * W + w];
+      }
+      store_record<W>(a.dst, pos, rec);
+    }
+    __syncthreads();
+  }
+}
+
+template <int W>
+static size_t rs_smem_bytes() {
+  return (size_t)RsCfg<W>::T * W * 8 + (2 * kRsMaxDigits + 8 + kRsMaxDigits + 1) * sizeof(unsigned int) + RsCfg<W>::T + 16;
+}
+
+template <int W, bool PASS_B>
+static int launch_radix_pass(const F8RadixArgs &a, int64_t tiles_bound, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CYL_CUDA(cudaFuncSetAttribute(fused8_radix_pass_kernel<W, PASS_B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<W>()));
+    attr_set = true;
+  }
+  int64_t grid = (int64_t)num_sms() * 2;
+  if (grid > tiles_bound) grid = tiles_bound < 1 ? 1 : tiles_bound;
+  fused8_radix_pass_kernel<W, PASS_B><<<(unsigned)grid, kRsThreads, rs_smem_bytes<W>(), s>>>(a);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+template <int W>
+static int radix_two_pass(F8RadixArgs a, uint64_t *tmp, uint64_t *rec, unsigned int *coarse_cursor, unsigned int *fine_cursor, cudaStream_t s) {
+  constexpr int T = RsCfg<W>::T;
+  {
+    ProfScope ps("fused_join_scatter_coarse", s);
+    a.dst = tmp;
+    a.cursor = coarse_cursor;
+    a.ndigits = a.ncoarse;
+    CYL_TRY((launch_radix_pass<W, false>(a, div_up(a.n, (int64_t)T), s)));
+  }
+  {
+    ProfScope ps("fused_join_scatter_fine", s);
+    a.src = tmp;
+    a.dst = rec;
+    a.cursor = fine_cursor;
+    a.ndigits = 1 << a.lo_bits;
+    CYL_TRY((launch_radix_pass<W, true>(a, div_up(a.n, (int64_t)T) + a.ncoarse, s)));
+  }
+  return CYL_OK;
+}
+
+// a.hist[bin] += rows of every bin (a.hist zeroed by the caller)
+static int f8_bin_histogram(const F8PartArgs &a, int64_t nbins, int64_t tile_guess, cudaStream_t s) {
+  if (nbins <= kBlkMaxBins) {  // histogram in shared memory, totals merged with one reduction per (tile, bin)
+    F8BlockArgs h;
+    memset(&h, 0, sizeof(h));
+    for (int c = 0; c < a.ncols; c++) h.cols[c] = a.cols[c];
+    h.key = a.key;
+    h.key_is_f64 = a.key_is_f64;
+    h.shift = a.shift;
+    h.n = a.n;
+    h.nbins = nbins;
+    int64_t tile = div_up(tile_guess < 8192 ? 8192 : tile_guess, (int64_t)kBlkThreads * kF8PartRows) * kBlkThreads * kF8PartRows;
+    h.tile_rows = tile;
+    h.nblocks = div_up(a.n, tile);
+    h.bin_total = a.hist;
+    static bool attr_set = false;
+    if (!attr_set) {
+      CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
+      attr_set = true;
+    }
+    ProfScope ps("fused_join_hist", s);
+    fused8_block_hist_kernel<<<(unsigned)h.nblocks, kBlkThreads, (size_t)nbins * sizeof(unsigned int), s>>>(h);
+    CYL_LAUNCH_CHECK();
+  } else {
+    ProfScope ps("fused_join_hist", s);
+    fused8_hist_kernel<<<f8_grid(a.n, 256 * kF8PartRows), 256, 0, s>>>(a);
+    CYL_LAUNCH_CHECK();
+  }
+  return CYL_OK;
+}
+
+static int f8_partition_two_pass(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_t nbins, int shift, uint64_t *rec,
+                                 int64_t *bin_off, cudaStream_t s) {
+  const int kb = 64 - shift;
+  const int hi_bits = (kb + 1) / 2 > 8 ? 8 : (kb + 1) / 2, lo_bits = kb - hi_bits;
+  F8PartArgs h;
+  memset(&h, 0, sizeof(h));
+  for (int c = 0; c < ncols; c++) h.cols[c] = static_cast<const uint64_t *>(cols[c].data);
+  h.ncols = ncols;
+  h.key = key;
+  h.key_is_f64 = cols[key].type == CYL_DOUBLE;
+  h.n = n;
+  h.shift = shift;
+  Scratch hist, fine, coarse, prefix, tmp;
+  CYL_TRY(hist.alloc((size_t)nbins * sizeof(unsigned int), s));
+  CYL_TRY(fine.alloc((size_t)nbins * sizeof(unsigned int), s));
+  CYL_TRY(coarse.alloc((size_t)kRsMaxDigits * sizeof(unsigned int), s));
+  CYL_TRY(prefix.alloc((size_t)(kRsMaxDigits + 1) * sizeof(unsigned int), s));
+  CYL_TRY(tmp.alloc((size_t)n * ncols * 8 + 16, s));
+  CYL_CUDA(cudaMemsetAsync(hist.p, 0, (size_t)nbins * sizeof(unsigned int), s));
+  h.hist = hist.as<unsigned int>();
+  CYL_TRY(f8_bin_histogram(h, nbins, n / ((int64_t)num_sms() * 4) + 1, s));
+  F8RadixArgs a;
+  memset(&a, 0, sizeof(a));
+  for (int c = 0; c < ncols; c++) a.cols[c] = h.cols[c];
+  a.cols_aligned16 = 1;
+  for (int c = 0; c < ncols; c++) a.cols_aligned16 &= (reinterpret_cast<uintptr_t>(a.cols[c]) & 15) == 0;
+  a.key = key;
+  a.key_is_f64 = h.key_is_f64;
+  a.shift = shift;
+  a.lo_bits = lo_bits;
+  a.n = n;
+  a.bin_off = bin_off;
+  a.ncoarse = 1 << hi_bits;
+  a.tile_prefix = prefix.as<unsigned int>();
+  const int tile_rows = ncols <= 2 ? RsCfg<2>::T : RsCfg<4>::T;
+  {
+    ProfScope ps("fused_join_offsets", s);
+    CYL_TRY(exclusive_scan<uint32_t>(hist.as<unsigned int>(), nbins, bin_off, s));
+    narrow_cursor_kernel<<<f8_grid(nbins, 256), 256, 0, s>>>(bin_off, nbins, fine.as<unsigned int>());
+    CYL_LAUNCH_CHECK();
+    fused8_coarse_cursor_kernel<<<1, kRsMaxDigits, 0, s>>>(bin_off, lo_bits, a.ncoarse, coarse.as<unsigned int>());
+    CYL_LAUNCH_CHECK();
+    fused8_tile_prefix_kernel<<<1, kRsMaxDigits + 32, 0, s>>>(bin_off, lo_bits, a.ncoarse, tile_rows, prefix.as<unsigned int>());
+    CYL_LAUNCH_CHECK();
+  }
+  switch (ncols) {
+    case 1: return radix_two_pass<1>(a, tmp.as<uint64_t>(), rec, coarse.as<unsigned int>(), fine.as<unsigned int>(), s);
+    case 2: return radix_two_pass<2>(a, tmp.as<uint64_t>(), rec, coarse.as<unsigned int>(), fine.as<unsigned int>(), s);
+    case 3: return radix_two_pass<3>(a, tmp.as<uint64_t>(), rec, coarse.as<unsigned int>(), fine.as<unsigned int>(), s);
+    default: return radix_two_pass<4>(a, tmp.as<uint64_t>(), rec, coarse.as<unsigned int>(), fine.as<unsigned int>(), s);
+  }
+}
+
 static int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_t nbins, int shift, uint64_t *rec, int64_t *bin_off,
                         cudaStream_t s) {
   // Measured on B200 at 100M rows x 32768 bins (profiles/r01_fused_join_notes.md): block-private cursors make the
@@ -435,6 +774,10 @@ static int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n,
   // So: block-private ranges only while a (tile, bin) run is long enough to fill lines, else shared cursors -- but
   // always the shared-memory histogram, which is 4x faster than global reductions.
   const int64_t tile_guess = n / ((int64_t)num_sms() * 4) + 1;
+  {  // large tables: two staged passes with coalesced stores instead of one pass of scattered stores
+    const int kb = 64 - shift;
+    if (kb >= 9 && kb <= 16 && n >= (int64_t)g_two_pass_min_rows && n < 0xFFFFFFFFll) return f8_partition_two_pass(cols, ncols, key, n, nbins, shift, rec, bin_off, s);
+  }
   if (nbins <= kBlkMaxBins && tile_guess / nbins >= 32) return f8_partition_blocks(cols, ncols, key, n, nbins, shift, rec, bin_off, s);
   F8PartArgs a;
   memset(&a, 0, sizeof(a));
@@ -451,32 +794,7 @@ static int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n,
   CYL_CUDA(cudaMemsetAsync(hist.p, 0, (size_t)nbins * sizeof(unsigned int), s));
   a.hist = hist.as<unsigned int>();
   a.cursor = cursor.as<unsigned int>();
-  if (nbins <= kBlkMaxBins) {  // histogram in shared memory, totals merged with one reduction per (tile, bin)
-    F8BlockArgs h;
-    memset(&h, 0, sizeof(h));
-    for (int c = 0; c < ncols; c++) h.cols[c] = a.cols[c];
-    h.key = key;
-    h.key_is_f64 = a.key_is_f64;
-    h.shift = shift;
-    h.n = n;
-    h.nbins = nbins;
-    int64_t tile = div_up(tile_guess < 8192 ? 8192 : tile_guess, (int64_t)kBlkThreads * kF8PartRows) * kBlkThreads * kF8PartRows;
-    h.tile_rows = tile;
-    h.nblocks = div_up(n, tile);
-    h.bin_total = a.hist;
-    static bool attr_set = false;
-    if (!attr_set) {
-      CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
-      attr_set = true;
-    }
-    ProfScope ps("fused_join_hist", s);
-    fused8_block_hist_kernel<<<(unsigned)h.nblocks, kBlkThreads, (size_t)nbins * sizeof(unsigned int), s>>>(h);
-    CYL_LAUNCH_CHECK();
-  } else {
-    ProfScope ps("fused_join_hist", s);
-    fused8_hist_kernel<<<f8_grid(n, 256 * kF8PartRows), 256, 0, s>>>(a);
-    CYL_LAUNCH_CHECK();
-  }
+  CYL_TRY(f8_bin_histogram(a, nbins, tile_guess, s));
   CYL_TRY(exclusive_scan<uint32_t>(hist.as<unsigned int>(), nbins, bin_off, s));
   narrow_cursor_kernel<<<f8_grid(nbins, 256), 256, 0, s>>>(bin_off, nbins, a.cursor);
   CYL_LAUNCH_CHECK();

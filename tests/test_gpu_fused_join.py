@@ -141,3 +141,23 @@ def test_fused_join_large(skew):
     general = L.join(R, "inner", "sort", [0], [0])
     assert general.row_count == m_ref and general.checksum() == cs_ref
     ctx.finalize()
+
+
+@pytest.mark.parametrize("wl,wr,fkey", [(1, 1, False), (2, 2, True), (3, 2, False), (4, 4, False), (2, 3, True)])
+def test_fused_join_two_pass_partition_widths(cy, wl, wr, fkey):
+    """Tables above 2^21 rows take the two-pass staged radix partition (coarse digit, then fine digit); every record
+    width 1-4 and a double key, ragged sizes, against the oracle's rows."""
+    rng = np.random.default_rng(wl * 10 + wr)
+    nl, nr = 2_300_017, 2_100_003
+    dom = 3_000_000
+
+    def table(n, w):
+        k = rng.integers(0, dom, n)
+        key = orc.col(k.astype(np.float64) - 0.5 * (k % 3 == 0)) if fkey else orc.col(k.astype(np.int64) - dom // 2)
+        return [key] + [orc.col(rng.random(n)) if i % 2 == 0 else orc.col(rng.integers(-2 ** 60, 2 ** 60, n).astype(np.int64)) for i in range(w - 1)]
+
+    l, r = table(nl, wl), table(nr, wr)
+    # key last on the left for wide tables: exercises the key-position select inside the record
+    if wl > 1:
+        l = l[1:] + l[:1]
+    _check(cy, l, r, wl - 1 if wl > 1 else 0, 0)
