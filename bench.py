@@ -116,6 +116,8 @@ def algorithmic_bytes(kernel, n, m):
         "fused_join_hist": n * 8,            # per launch (one table): keys in
         "fused_join_offsets": 0,
         "fused_join_scatter": n * 16 * 2,    # per launch (one table): (key, payload) columns in + packed records out
+        "fused_join_scatter_coarse": n * 16 * 2,  # per launch (one table): columns in + records ordered by coarse digit out
+        "fused_join_scatter_fine": n * 16 * 2,    # per launch (one table): records in + records ordered by bin out
         "fused_join_probe": 2 * n * 16 + m * 32,  # both record streams in + the 4 result columns out (= SURVEY 8d local join)
         "partition_scatter_peer": n * 16 * 2,  # per launch (one table): rows in + rows out (remote share over NVLink)
         "partition_tile_hist": n * 8,
@@ -204,6 +206,7 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=4_000_000, help="rows per side of the CPU baseline sample")
     ap.add_argument("--ref-rows", type=int, default=2_000_000, help="--impl reference: rows per side per rank")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-lanes", type=int, default=3, help="N=1 only: steps kept in flight by the e2e arm (one host thread + stream each)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -286,34 +289,69 @@ def main():
         host_out = [capi.pinned_array(cap, np.int64), capi.pinned_array(cap, np.float64), capi.pinned_array(cap, np.int64),
                     capi.pinned_array(cap, np.float64)]
 
-        def e2e_step():
-            l = api.Table.from_numpy(ctx, [lk, lv], names=["k", "v"])
-            r = api.Table.from_numpy(ctx, [rk, rv], names=["k", "v"])
+        def e2e_step(cx=ctx, outs=host_out):
+            l = api.Table.from_numpy(cx, [lk, lv], names=["k", "v"])
+            r = api.Table.from_numpy(cx, [rk, rv], names=["k", "v"])
             out = l.distributed_join(r, "inner", "hash", [0], [0], "l_", "r_")
             mm = out.row_count
             assert mm <= cap
             for c in range(4):
-                capi.check(capi.lib().cylon_table_column_to_host(out._h, C.c_int32(c), C.c_void_p(host_out[c].ctypes.data), None, None))
+                capi.check(capi.lib().cylon_table_column_to_host(out._h, C.c_int32(c), C.c_void_p(outs[c].ctypes.data), None, None))
             out.free()
             l.free()
             r.free()
             return mm
 
-        e2e_step()
+        # One GPU: two steps in flight. Two host threads, each with its own CylonContext on its own stream and its own
+        # pinned result buffers, take alternate steps, so one step's result download (PCIe up) overlaps the next step's
+        # input upload (PCIe down). Every step still uploads all of its inputs and downloads its whole result inside
+        # the timed region. With torchrun (N > 1) steps stay strictly one after another on the single NCCL communicator.
+        lanes = [(ctx, host_out)]
+        lane_streams = []
+        if world == 1 and args.steps >= 2:
+            import threading
+            for _ in range(1, max(1, min(args.e2e_lanes, args.steps))):
+                cx = api.CylonContext(device=local_rank)
+                lane_streams.append(torch.cuda.Stream())
+                cx.set_stream(lane_streams[-1].cuda_stream)
+                lanes.append((cx, [capi.pinned_array(cap, a.dtype) for a in host_out]))
+        for cx, outs in lanes:
+            e2e_step(cx, outs)
         barrier()
-        ev0.record()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
-            mm = e2e_step()
-        ev1.record()
-        barrier()
-        wall_ms = 1e3 * (time.perf_counter() - t0)
-        te = torch.tensor([max(ev0.elapsed_time(ev1), wall_ms)], dtype=torch.float64, device="cuda")
+        if len(lanes) == 1:
+            ev0.record()
+            for _ in range(args.steps):
+                mm = e2e_step()
+            ev1.record()
+            barrier()
+            wall_ms = max(ev0.elapsed_time(ev1), 1e3 * (time.perf_counter() - t0))
+        else:
+            got = [0] * len(lanes)
+
+            def lane_main(li):
+                torch.cuda.set_device(local_rank)  # the CUDA current device is per host thread
+                for sidx in range(li, args.steps, len(lanes)):
+                    got[li] = e2e_step(*lanes[li])
+
+            threads = [threading.Thread(target=lane_main, args=(li,)) for li in range(len(lanes))]
+            for th in threads:
+                th.start()
+            for th in threads:
+                th.join()
+            torch.cuda.synchronize()
+            wall_ms = 1e3 * (time.perf_counter() - t0)  # host clock around all K steps: spans both streams
+            mm = got[0]
+            assert all(g == mm for g in got)
+            for cx, _ in lanes[1:]:
+                cx.finalize()
+        te = torch.tensor([wall_ms], dtype=torch.float64, device="cuda")
         if dist is not None:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e_ms = float(te.item()) / args.steps
         e2e = {"value": 2.0 * rows * world / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(2 * rows * 16),
-               "d2h_bytes_per_step": int(mm * 32), "ms_per_step": e2e_ms}
+               "d2h_bytes_per_step": int(mm * 32), "ms_per_step": e2e_ms, "steps_in_flight": len(lanes),
+               "timed_with": "host clock around all steps, device synchronised on both sides"}
 
     sampler.stop_flag.set()
     if rank != 0:
@@ -341,6 +379,7 @@ def main():
         # dram__bytes_read+write per launch from the committed `ncu --set full` capture (only valid for the size it was taken at)
         traffic = None
         scope_to_kernel = {"fused_join_scatter": "void fused8_scatter_kernel<2>", "fused_join_probe": "void fused8_join_kernel<2, 2>",
+                           "fused_join_scatter_coarse": "void fused8_radix_pass_kernel<2, 0>", "fused_join_scatter_fine": "void fused8_radix_pass_kernel<2, 1>",
                            "fused_join_hist": "fused8_block_hist_kernel"}
         try:
             if rows == 100_000_000:

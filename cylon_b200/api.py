@@ -29,6 +29,7 @@ class CylonContext:
 
     def __init__(self, device=0, distributed=False, rank=0, world_size=1, nccl_id=None):
         self._h = C.c_void_p()
+        self._stream = None
         if distributed:
             if nccl_id is None or len(nccl_id) != 128:
                 raise ValueError("distributed context needs the 128-byte NCCL unique id created on rank 0")
@@ -38,7 +39,9 @@ class CylonContext:
             check(lib().cylon_context_init(C.c_int32(device), C.byref(self._h)))
 
     def set_stream(self, cuda_stream):
+        """All operators of tables created on this context run (and synchronise) on `cuda_stream`."""
         check(lib().cylon_context_set_stream(self._h, C.c_void_p(cuda_stream)))
+        self._stream = cuda_stream
 
     def get_rank(self):
         return lib().cylon_context_rank(self._h)
@@ -123,7 +126,7 @@ class Table:
             cnames = (C.c_char_p * n)(*[str(x).encode() for x in names])
         h = C.c_void_p()
         check(lib().cylon_table_from_host(ctx._h, arr, cnames, C.c_int32(n), C.byref(h)))
-        capi.sync(None)
+        capi.sync(ctx._stream)  # the host arrays may be reused as soon as this returns
         return cls(h, ctx)
 
     @classmethod
