@@ -323,6 +323,12 @@ int cyl_hash_join_fused_supported(const cyl_column_t *lcols, int32_t nlcols, int
   return plan_smem(lcols, nlcols, &pl) && plan_smem(rcols, nrcols, &pl) ? 1 : 0;
 }
 
+int cyl_hash_join_fused_set_bins_log2(int32_t bits) {
+  if (bits < 0 || bits > 18) return fail(CYL_Invalid, "cyl_hash_join_fused_set_bins_log2: bits must be in [0, 18], got %d", bits);
+  fused8_force_bins_log2(bits);
+  return CYL_OK;
+}
+
 int cyl_hash_join_fused_inner(const cyl_column_t *lcols, int32_t nlcols, int32_t lkey, const cyl_column_t *rcols, int32_t nrcols, int32_t rkey,
                               int64_t nl, int64_t nr, int64_t capacity, void *const *out_cols, int64_t *num_rows, void *stream) {
   cudaStream_t s = (cudaStream_t)stream;

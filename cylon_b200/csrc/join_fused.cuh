@@ -8,4 +8,6 @@ bool fused8_eligible(const cyl_column_t *lcols, int nlcols, const cyl_column_t *
 // build side b*, probe side p*; bout/pout: output column pointers of each side (capacity rows each)
 int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const cyl_column_t *pcols, int npc, int pkey, int64_t np,
                 void *const *bout, void *const *pout, int64_t capacity, int64_t *num_rows, cudaStream_t s);
+// Test hook: force 2^bits bins in fused8_join (0 = choose from the build size). More bins than needed is always valid.
+void fused8_force_bins_log2(int bits);
 }  // namespace cylb

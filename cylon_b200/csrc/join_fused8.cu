@@ -282,6 +282,7 @@ struct F8BlockArgs {
   const uint64_t *cols[kFused8MaxCols];
   int32_t key, key_is_f64, shift;
   int64_t n, tile_rows, nbins, nblocks;
+  int64_t bin_lo;                // histogram mode: only bins [bin_lo, bin_lo + nbins) are counted
   unsigned int *counts;          // [nblocks][nbins]
   const int64_t *bin_off;        // [nbins + 1]
   unsigned int *bin_total;       // [nbins]
@@ -304,7 +305,10 @@ __global__ void __launch_bounds__(kBlkThreads) fused8_block_hist_kernel(const __
     }
 #pragma unroll
     for (int u = 0; u < kF8PartRows; u++)
-      if (i0 + (int64_t)u * kBlkThreads < r1) atomicAdd(&s_cnt[f8_bin(f8_canon(k[u], a.key_is_f64), a.shift)], 1u);
+      if (i0 + (int64_t)u * kBlkThreads < r1) {
+        const uint32_t b = f8_bin(f8_canon(k[u], a.key_is_f64), a.shift) - (uint32_t)a.bin_lo;
+        if (b < (uint32_t)a.nbins) atomicAdd(&s_cnt[b], 1u);
+      }
   }
   __syncthreads();
   if (a.counts) {  // block-private cursors: keep the tile's counters as one coalesced row
@@ -432,8 +436,10 @@ static int f8_partition_blocks(const cyl_column_t *cols, int ncols, int key, int
 // atomicAdd per (tile, digit) on cursors preset from the full K-bin histogram -- row order inside a bin is arbitrary,
 // as it already was. All of a tile's loads are issued before the first use.
 constexpr int kRsThreads = 256;
+static int g_force_bins_log2 = 0;
+void fused8_force_bins_log2(int bits) { g_force_bins_log2 = bits; }
 static int64_t g_two_pass_min_rows = 1 << 21;  // below this the launch count matters more than the store pattern
-constexpr int kRsMaxDigits = 256;
+constexpr int kRsMaxDigits = 512;  // two digits per thread in the per-tile scan
 
 struct F8RadixArgs {
   const uint64_t *cols[kFused8MaxCols];  // pass A input (columns)
@@ -479,11 +485,10 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
   constexpr int T = RsCfg<W>::T;
   extern __shared__ __align__(16) unsigned char rs_smem[];
   uint64_t *stage = reinterpret_cast<uint64_t *>(rs_smem);                     // [T][W]
-  unsigned int *cnt = reinterpret_cast<unsigned int *>(stage + (size_t)T * W);  // [256] rows per digit, then run starts
-  unsigned int *delta = cnt + kRsMaxDigits;                                     // [256] destination - staging slot
+  unsigned int *cnt = reinterpret_cast<unsigned int *>(stage + (size_t)T * W);  // [512] rows per digit, then run starts
+  unsigned int *delta = cnt + kRsMaxDigits;                                     // [512] destination - staging slot
   unsigned int *warp_tot = delta + kRsMaxDigits;                                // [8]
-  unsigned int *prefix = warp_tot + 8;                                          // [257] (pass B)
-  uint8_t *slot_digit = reinterpret_cast<uint8_t *>(prefix + kRsMaxDigits + 1); // [T]
+  unsigned int *prefix = warp_tot + 8;                                          // [513] (pass B)
   const int tid = threadIdx.x;
   const unsigned lane = tid & 31, warp = tid >> 5;
   const uint32_t lo_mask = (1u << a.lo_bits) - 1;
@@ -570,7 +575,8 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
     load_tile(r0, r1);
   }
   for (int64_t g = blockIdx.x; g < ntiles; g += gridDim.x) {
-    cnt[tid] = 0;
+    cnt[2 * tid] = 0;
+    cnt[2 * tid + 1] = 0;
     __syncthreads();  // counters are zero
     uint32_t dr[R];   // digit << 16 | rank inside the (tile, digit) run
 #pragma unroll
@@ -582,7 +588,7 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
     }
     __syncthreads();
     {  // exclusive scan of the 256 counters; digit `tid` reserves its run's destination range
-      const unsigned int c = cnt[tid];
+      const unsigned int c0 = cnt[2 * tid], c1 = cnt[2 * tid + 1], c = c0 + c1;
       unsigned int inc = c;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -590,15 +596,18 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
         if (lane >= (unsigned)d) inc += t;
       }
       if (lane == 31) warp_tot[warp] = inc;
-      unsigned int g0 = 0;
-      if (c) g0 = atomicAdd(&a.cursor[cursor_base + tid], c);
+      unsigned int g0 = 0, g1 = 0;
+      if (c0) g0 = atomicAdd(&a.cursor[cursor_base + 2 * tid], c0);
+      if (c1) g1 = atomicAdd(&a.cursor[cursor_base + 2 * tid + 1], c1);
       __syncthreads();
       unsigned int before = 0;
 #pragma unroll
       for (int w = 0; w < kRsThreads / 32; w++) before += w < (int)warp ? warp_tot[w] : 0u;
-      const unsigned int start = before + inc - c;
-      cnt[tid] = start;
-      delta[tid] = g0 - start;
+      const unsigned int start0 = before + inc - c, start1 = start0 + c0;
+      cnt[2 * tid] = start0;
+      cnt[2 * tid + 1] = start1;
+      delta[2 * tid] = g0 - start0;
+      delta[2 * tid + 1] = g1 - start1;
     }
     __syncthreads();
 #pragma unroll
@@ -611,7 +620,6 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
 #pragma unroll
           for (int w = 0; w < W; w++) stage[(size_t)slot * W + w] = v[u][w];
         }
-        slot_digit[slot] = (uint8_t)d;
       }
     }
     const int nvalid = (int)(r1 - r0);
@@ -621,8 +629,6 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
     }
     __syncthreads();
     for (int j = tid; j < nvalid; j += kRsThreads) {  // consecutive threads -> consecutive records of a run
-      const uint32_t d = slot_digit[j];
-      const uint32_t pos = delta[d] + (uint32_t)j;
       uint64_t rec[W];
       if constexpr (W == 2) {
         const ulonglong2 t = *reinterpret_cast<const ulonglong2 *>(stage + (size_t)j * 2);
@@ -632,7 +638,11 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
 #pragma unroll
         for (int w = 0; w < W; w++) rec[w] = stage[(size_t)j * W + w];
       }
-      store_record<W>(a.dst, pos, rec);
+      // the run a slot belongs to = the digit of its key, recomputed: a few ALU instructions instead of a per-slot
+      // digit array in shared memory (measured the same; shared memory is the busy resource of this kernel)
+      const uint32_t bin = f8_bin(f8_canon(f8_pick<W>(rec, a.key), a.key_is_f64), a.shift);
+      const uint32_t d = PASS_B ? (bin & lo_mask) : (bin >> a.lo_bits);
+      store_record<W>(a.dst, delta[d] + (uint32_t)j, rec);
     }
     __syncthreads();
   }
@@ -640,7 +650,7 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
 
 template <int W>
 static size_t rs_smem_bytes() {
-  return (size_t)RsCfg<W>::T * W * 8 + (2 * kRsMaxDigits + 8 + kRsMaxDigits + 1) * sizeof(unsigned int) + RsCfg<W>::T + 16;
+  return (size_t)RsCfg<W>::T * W * 8 + (2 * kRsMaxDigits + 8 + kRsMaxDigits + 1) * sizeof(unsigned int) + 16;
 }
 
 template <int W, bool PASS_B>
@@ -701,6 +711,32 @@ static int f8_bin_histogram(const F8PartArgs &a, int64_t nbins, int64_t tile_gue
     ProfScope ps("fused_join_hist", s);
     fused8_block_hist_kernel<<<(unsigned)h.nblocks, kBlkThreads, (size_t)nbins * sizeof(unsigned int), s>>>(h);
     CYL_LAUNCH_CHECK();
+  } else if (nbins == 2 * kBlkMaxBins) {
+    // 65536 bins do not fit one CTA's shared memory: two launches, each counting one half of the bin range and reading
+    // all keys (2 x 0.2 ms per 100 M rows; reductions straight into HBM cost 0.74 ms)
+    F8BlockArgs h;
+    memset(&h, 0, sizeof(h));
+    for (int c = 0; c < a.ncols; c++) h.cols[c] = a.cols[c];
+    h.key = a.key;
+    h.key_is_f64 = a.key_is_f64;
+    h.shift = a.shift;
+    h.n = a.n;
+    h.nbins = kBlkMaxBins;
+    int64_t tile = div_up(tile_guess < 8192 ? 8192 : tile_guess, (int64_t)kBlkThreads * kF8PartRows) * kBlkThreads * kF8PartRows;
+    h.tile_rows = tile;
+    h.nblocks = div_up(a.n, tile);
+    static bool attr_set2 = false;
+    if (!attr_set2) {
+      CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
+      attr_set2 = true;
+    }
+    ProfScope ps("fused_join_hist", s);
+    for (int half = 0; half < 2; half++) {
+      h.bin_lo = half * kBlkMaxBins;
+      h.bin_total = a.hist + half * kBlkMaxBins;
+      fused8_block_hist_kernel<<<(unsigned)h.nblocks, kBlkThreads, (size_t)kBlkMaxBins * sizeof(unsigned int), s>>>(h);
+      CYL_LAUNCH_CHECK();
+    }
   } else {
     ProfScope ps("fused_join_hist", s);
     fused8_hist_kernel<<<f8_grid(a.n, 256 * kF8PartRows), 256, 0, s>>>(a);
@@ -712,7 +748,7 @@ static int f8_bin_histogram(const F8PartArgs &a, int64_t nbins, int64_t tile_gue
 static int f8_partition_two_pass(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_t nbins, int shift, uint64_t *rec,
                                  int64_t *bin_off, cudaStream_t s) {
   const int kb = 64 - shift;
-  const int hi_bits = (kb + 1) / 2 > 8 ? 8 : (kb + 1) / 2, lo_bits = kb - hi_bits;
+  const int hi_bits = (kb + 1) / 2, lo_bits = kb - hi_bits;  // each <= 9 = log2(kRsMaxDigits)
   F8PartArgs h;
   memset(&h, 0, sizeof(h));
   for (int c = 0; c < ncols; c++) h.cols[c] = static_cast<const uint64_t *>(cols[c].data);
@@ -776,7 +812,7 @@ static int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n,
   const int64_t tile_guess = n / ((int64_t)num_sms() * 4) + 1;
   {  // large tables: two staged passes with coalesced stores instead of one pass of scattered stores
     const int kb = 64 - shift;
-    if (kb >= 9 && kb <= 16 && n >= (int64_t)g_two_pass_min_rows && n < 0xFFFFFFFFll) return f8_partition_two_pass(cols, ncols, key, n, nbins, shift, rec, bin_off, s);
+    if (kb >= 9 && kb <= 18 && n >= (int64_t)g_two_pass_min_rows && n < 0xFFFFFFFFll) return f8_partition_two_pass(cols, ncols, key, n, nbins, shift, rec, bin_off, s);
   }
   if (nbins <= kBlkMaxBins && tile_guess / nbins >= 32) return f8_partition_blocks(cols, ncols, key, n, nbins, shift, rec, bin_off, s);
   F8PartArgs a;
@@ -856,6 +892,7 @@ int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const 
   }
   int64_t nbins = 1;
   while (nbins * (int64_t)(cap * 8 / 10) < nb && nbins < (1ll << 22)) nbins *= 2;
+  if (g_force_bins_log2 > 0) nbins = 1ll << g_force_bins_log2;  // test hook: more (smaller) bins than the size asks for
   int bits = 0;
   while ((1ll << bits) < nbins) bits++;
   const int shift = 64 - bits;

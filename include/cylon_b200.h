@@ -169,6 +169,11 @@ int cyl_hash_join_fused_supported(const cyl_column_t *lcols /* host array */, in
 int cyl_hash_join_fused_inner(const cyl_column_t *lcols /* host array */, int32_t nlcols, int32_t lkey, const cyl_column_t *rcols /* host array */,
                               int32_t nrcols, int32_t rkey, int64_t nl, int64_t nr, int64_t capacity, void *const *out_cols /* host array */,
                               int64_t *num_rows /* host out */, void *stream);
+/* Tuning/test hook with no reference counterpart: force 2^bits radix bins (1..18) in the all-8-byte fused join instead of
+ * the count chosen from the build size; 0 restores the automatic choice. More bins than needed is always valid (they
+ * are just emptier), so tests use it to reach the many-bin code paths (512-way digits, split histogram) with small
+ * tables. Process-wide; do not change it while a join is running. Returns CYL_Invalid outside 0..18. */
+int cyl_hash_join_fused_set_bins_log2(int32_t bits);
 
 /* ---------------------------------------------------------------- D4: gather ------------------- */
 /* dst[i] = idx[i] < 0 ? 0 : src[idx[i]]; dst_validity (may be NULL) gets bit i = (idx[i] >= 0), it has

@@ -161,3 +161,19 @@ def test_fused_join_two_pass_partition_widths(cy, wl, wr, fkey):
     if wl > 1:
         l = l[1:] + l[:1]
     _check(cy, l, r, wl - 1 if wl > 1 else 0, 0)
+
+
+@pytest.mark.parametrize("bits", [9, 13, 16, 17, 18])
+def test_fused_join_forced_bin_counts(cy, bits):
+    """The many-bin code paths with a table that fits a test: 2^9 (5+4-bit digits) .. 2^18 bins (9+9-bit digits, i.e.
+    512-way passes), 2^16 (histogram counted in two half-range launches), 2^17+ (histogram by global reductions)."""
+    rng = np.random.default_rng(bits)
+    nl, nr, dom = 2_200_013, 2_150_001, 2_500_000
+    l = [orc.col(rng.integers(0, dom, nl).astype(np.int64)), orc.col(rng.random(nl))]
+    r = [orc.col(rng.integers(0, dom, nr).astype(np.int64)), orc.col(rng.random(nr))]
+    cy.check(cy.lib().cyl_hash_join_fused_set_bins_log2(bits))
+    try:
+        _check(cy, l, r, 0, 0)
+    finally:
+        cy.check(cy.lib().cyl_hash_join_fused_set_bins_log2(0))
+    assert cy.lib().cyl_hash_join_fused_set_bins_log2(19) != 0
