@@ -18,4 +18,8 @@ fi
 if [ -x "$HERE/ref_shim/build_cylon_ref.sh" ]; then
   "$HERE/ref_shim/build_cylon_ref.sh" "$OUT" || echo "build_ref: reference join library not built (see DESIGN.md)"
 fi
+# 3. aggregation kernels (header-only in the reference: compute/aggregate_kernels.hpp), Arrow-free
+if [ ! -f "$OUT/libref_aggregate.so" ] || [ "$HERE/ref_shim/aggregate_shim.cpp" -nt "$OUT/libref_aggregate.so" ]; then
+  $CXX -O2 -fPIC -shared -std=c++17 -I"$REF" -o "$OUT/libref_aggregate.so" "$HERE/ref_shim/aggregate_shim.cpp"
+fi
 echo "build_ref: ok"

@@ -113,3 +113,31 @@ def join_tables(left, right, lkeys, rkeys, join_type, algorithm):
         out.append(col)
     lib().ref_table_free(h)
     return out
+
+
+# ---- the reference's aggregation kernels (compute/aggregate_kernels.hpp, compiled by oracle/build_ref.sh) ------------
+_AGG_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_aggregate.so")
+_agg_lib = None
+_AGG_DTYPES = {"int8": 0, "int16": 1, "int32": 2, "int64": 3, "uint8": 4, "uint16": 5, "uint32": 6, "uint64": 7, "float32": 8, "float64": 9}
+
+
+def aggregate_available():
+    return os.path.exists(_AGG_PATH)
+
+
+def ref_aggregate(op, values, gid, num_groups):
+    """SumKernel / MinKernel / MaxKernel / CountKernel of the reference driven as groupby/hash_groupby.cpp:142-201
+    drives them. op = orc.SUM/MIN/MAX/COUNT (same values as the reference's AggregationOpId)."""
+    global _agg_lib
+    if _agg_lib is None:
+        _agg_lib = C.CDLL(_AGG_PATH)
+    values = np.ascontiguousarray(values)
+    gid = np.ascontiguousarray(gid, dtype=np.int64)
+    out = np.zeros(max(1, num_groups), dtype=np.int64 if op == orc.COUNT else values.dtype)
+    v = values if values.size else np.zeros(1, dtype=values.dtype)
+    g = gid if gid.size else np.zeros(1, dtype=np.int64)
+    rc = _agg_lib.ref_aggregate(int(op), _AGG_DTYPES[values.dtype.name], v.ctypes.data_as(C.c_void_p), g.ctypes.data_as(C.c_void_p),
+                                C.c_int64(len(values)), C.c_int64(num_groups), out.ctypes.data_as(C.c_void_p))
+    if rc != 0:
+        raise RuntimeError("ref_aggregate failed: %d" % rc)
+    return out[:num_groups]

@@ -71,3 +71,32 @@ def test_join_tables_match_reference(algo, jt, keys):
     exp = pyref.join_tables(l, r, keys, keys, jt, algo)
     got = orc.join(l, r, keys, keys, jt, algo)
     assert_same_rows(got, exp, "algo %d type %d keys %s" % (algo, jt, keys))
+
+
+# ---- G2/G3: the reference's aggregation kernels themselves (compute/aggregate_kernels.hpp compiled in place) ----------
+_AGG_KINDS = ["int8", "int16", "int32", "int64", "uint8", "uint16", "uint32", "uint64", "float32", "float64"]
+
+
+@pytest.mark.skipif(not pyref.aggregate_available(), reason="oracle/_ref/libref_aggregate.so not built")
+@pytest.mark.parametrize("kind", _AGG_KINDS)
+@pytest.mark.parametrize("op", [orc.SUM, orc.MIN, orc.MAX, orc.COUNT])
+def test_aggregate_matches_reference_kernels(kind, op):
+    """SUM in the column's own C type (integers wrap), COUNT as int64, MIN from numeric_limits<T>::max(), MAX from
+    numeric_limits<T>::min() -- for float/double the smallest positive normal, so an all-negative group reports it."""
+    rng = np.random.default_rng(_AGG_KINDS.index(kind) * 10 + op)
+    n, groups = 5000, 37
+    dt = np.dtype(kind)
+    if dt.kind == "f":
+        vals = ((rng.random(n) - 0.5) * 1e6).astype(dt)
+    else:
+        info = np.iinfo(dt)
+        vals = rng.integers(info.min, info.max, n, dtype=dt, endpoint=True)  # full range: sums wrap around
+    gid = rng.integers(0, groups - 2, n)  # the last two groups stay empty: initial states are reported as they are
+    if dt.kind == "f":
+        vals[gid == 3] = -np.abs(vals[gid == 3]) - 1  # an all-negative group (G3: MAX returns DBL_MIN / FLT_MIN)
+    got = orc.aggregate(orc.col(vals), gid, groups, op)
+    exp = pyref.ref_aggregate(op, vals, gid, groups)
+    assert got.dtype == exp.dtype
+    assert np.array_equal(got, exp)  # floating-point SUM too: same sequential order of additions as the reference
+    if dt.kind == "f" and op == orc.MAX:
+        assert exp[3] == np.finfo(dt).tiny
