@@ -435,11 +435,12 @@ static int f8_partition_blocks(const cyl_column_t *cols, int ncols, int key, int
 // pass of scattered stores. Slots inside a run come from shared-memory atomics, ranges inside a bin from one global
 // atomicAdd per (tile, digit) on cursors preset from the full K-bin histogram -- row order inside a bin is arbitrary,
 // as it already was. All of a tile's loads are issued before the first use.
-constexpr int kRsThreads = 256;
+constexpr int kRsThreads = 512;  // == kRsMaxDigits: one digit per thread in the per-tile scan
 static int g_force_bins_log2 = 0;
 void fused8_force_bins_log2(int bits) { g_force_bins_log2 = bits; }
 static int64_t g_two_pass_min_rows = 1 << 21;  // below this the launch count matters more than the store pattern
-constexpr int kRsMaxDigits = 512;  // two digits per thread in the per-tile scan
+constexpr int kRsMaxDigits = 512;
+static_assert(kRsThreads == kRsMaxDigits, "the per-tile scan maps one digit to one thread");
 
 struct F8RadixArgs {
   const uint64_t *cols[kFused8MaxCols];  // pass A input (columns)
@@ -455,7 +456,7 @@ struct F8RadixArgs {
 
 template <int W>
 struct RsCfg {
-  static constexpr int R = W <= 2 ? 16 : 8;  // rows per thread
+  static constexpr int R = W <= 2 ? 8 : 4;   // rows per thread
   static constexpr int T = R * kRsThreads;   // rows per tile: 64 KB of records for W = 2 and W = 4
 };
 
@@ -487,8 +488,8 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
   uint64_t *stage = reinterpret_cast<uint64_t *>(rs_smem);                     // [T][W]
   unsigned int *cnt = reinterpret_cast<unsigned int *>(stage + (size_t)T * W);  // [512] rows per digit, then run starts
   unsigned int *delta = cnt + kRsMaxDigits;                                     // [512] destination - staging slot
-  unsigned int *warp_tot = delta + kRsMaxDigits;                                // [8]
-  unsigned int *prefix = warp_tot + 8;                                          // [513] (pass B)
+  unsigned int *warp_tot = delta + kRsMaxDigits;                                // [16]
+  unsigned int *prefix = warp_tot + kRsThreads / 32;                                          // [513] (pass B)
   const int tid = threadIdx.x;
   const unsigned lane = tid & 31, warp = tid >> 5;
   const uint32_t lo_mask = (1u << a.lo_bits) - 1;
@@ -575,8 +576,7 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
     load_tile(r0, r1);
   }
   for (int64_t g = blockIdx.x; g < ntiles; g += gridDim.x) {
-    cnt[2 * tid] = 0;
-    cnt[2 * tid + 1] = 0;
+    cnt[tid] = 0;
     __syncthreads();  // counters are zero
     uint32_t dr[R];   // digit << 16 | rank inside the (tile, digit) run
 #pragma unroll
@@ -588,7 +588,7 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
     }
     __syncthreads();
     {  // exclusive scan of the 256 counters; digit `tid` reserves its run's destination range
-      const unsigned int c0 = cnt[2 * tid], c1 = cnt[2 * tid + 1], c = c0 + c1;
+      const unsigned int c = cnt[tid];
       unsigned int inc = c;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -596,18 +596,15 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
         if (lane >= (unsigned)d) inc += t;
       }
       if (lane == 31) warp_tot[warp] = inc;
-      unsigned int g0 = 0, g1 = 0;
-      if (c0) g0 = atomicAdd(&a.cursor[cursor_base + 2 * tid], c0);
-      if (c1) g1 = atomicAdd(&a.cursor[cursor_base + 2 * tid + 1], c1);
+      unsigned int g0 = 0;
+      if (c) g0 = atomicAdd(&a.cursor[cursor_base + tid], c);
       __syncthreads();
       unsigned int before = 0;
 #pragma unroll
       for (int w = 0; w < kRsThreads / 32; w++) before += w < (int)warp ? warp_tot[w] : 0u;
-      const unsigned int start0 = before + inc - c, start1 = start0 + c0;
-      cnt[2 * tid] = start0;
-      cnt[2 * tid + 1] = start1;
-      delta[2 * tid] = g0 - start0;
-      delta[2 * tid + 1] = g1 - start1;
+      const unsigned int start = before + inc - c;
+      cnt[tid] = start;
+      delta[tid] = g0 - start;
     }
     __syncthreads();
 #pragma unroll
@@ -650,7 +647,7 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
 
 template <int W>
 static size_t rs_smem_bytes() {
-  return (size_t)RsCfg<W>::T * W * 8 + (2 * kRsMaxDigits + 8 + kRsMaxDigits + 1) * sizeof(unsigned int) + 16;
+  return (size_t)RsCfg<W>::T * W * 8 + (2 * kRsMaxDigits + kRsThreads / 32 + kRsMaxDigits + 1) * sizeof(unsigned int) + 16;
 }
 
 template <int W, bool PASS_B>
