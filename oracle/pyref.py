@@ -115,6 +115,58 @@ def join_tables(left, right, lkeys, rkeys, join_type, algorithm):
     return out
 
 
+def _table_out(h):
+    """ref_table handle -> oracle-style table (list of HCol with the reference's column names); frees the handle."""
+    L = lib()
+    L.ref_table_col_name.restype = C.c_char_p
+    n, ncols = L.ref_table_rows(h), L.ref_table_cols(h)
+    out = []
+    for c in range(ncols):
+        t = L.ref_table_col_type(h, c)
+        name = L.ref_table_col_name(h, c).decode()
+        nbytes = L.ref_table_col_bytes(h, c)
+        valid = np.ones(max(1, n), dtype=np.uint8)
+        if t in (orc.STRING, orc.BINARY):
+            data = np.zeros(max(1, nbytes), dtype=np.uint8)
+            offs = np.zeros(n + 1, dtype=np.int32)
+            L.ref_table_copy_col(h, c, C.c_void_p(data.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_void_p(valid.ctypes.data))
+            col = orc.HCol(t, data[:nbytes], offs, name=name)
+        else:
+            data = np.zeros(max(1, n), dtype=orc._TYPE2NP[t])
+            L.ref_table_copy_col(h, c, C.c_void_p(data.ctypes.data), None, C.c_void_p(valid.ctypes.data))
+            col = orc.HCol(t, data[:n], name=name)
+        v = valid[:n].astype(bool)
+        if not v.all():
+            col.validity = np.packbits(v, bitorder="little")
+        out.append(col)
+    L.ref_table_free(h)
+    return out
+
+
+DIST_JOIN, DIST_UNION, DIST_SUBTRACT, DIST_INTERSECT, DIST_UNIQUE, DIST_SHUFFLE, DIST_GROUPBY = range(7)
+
+
+def dist_op(op, lefts, rights=None, p1=(), p2=(), join_type=0, algorithm=0):
+    """One Distributed* operator of the reference on len(lefts) ranks (threads inside this process, an in-memory
+    Communicator/Channel in place of MPI). lefts / rights: one oracle-style table per rank. -> one table per rank."""
+    world = len(lefts)
+    nlc = len(lefts[0])
+    flat_l = [c for t in lefts for c in t]
+    la, _k1 = _table_in(flat_l)
+    nrc, ra, _k2 = 0, None, None
+    if rights is not None:
+        nrc = len(rights[0])
+        ra, _k2 = _table_in([c for t in rights for c in t])
+    a1 = (C.c_int32 * max(1, len(p1)))(*p1)
+    a2 = (C.c_int32 * max(1, len(p2)))(*p2)
+    outs = (C.c_void_p * world)()
+    rc = lib().ref_dist_op(C.c_int32(op), C.c_int32(world), la, C.c_int32(nlc), ra, C.c_int32(nrc), a1, C.c_int32(len(p1)), a2,
+                           C.c_int32(len(p2)), C.c_int32(join_type), C.c_int32(algorithm), outs)
+    if rc != 0:
+        raise RuntimeError("reference operator failed with cylon::Code %d" % rc)
+    return [_table_out(C.c_void_p(outs[r])) for r in range(world)]
+
+
 # ---- the reference's aggregation kernels (compute/aggregate_kernels.hpp, compiled by oracle/build_ref.sh) ------------
 _AGG_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_aggregate.so")
 _agg_lib = None

@@ -10,7 +10,21 @@
 #include <memory>
 #include <vector>
 
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <map>
+#include <mutex>
+#include <thread>
+
 #include "arrow/arrow_partition_kernels.hpp"
+#include "ctx/cylon_context.hpp"
+#include "groupby/groupby.hpp"
+#include "groupby/pipeline_groupby.hpp"
+#include "io/arrow_io.hpp"
+#include "net/channel.hpp"
+#include "net/communicator.hpp"
+#include "table.hpp"
 #include "join/hash_join.hpp"
 #include "join/join.hpp"
 #include "arrow/arrow_types.hpp"
@@ -46,10 +60,46 @@ arrow::Status copy_array_by_indices(const std::vector<int64_t> &indices, const s
 }
 }  // namespace util
 arrow::MemoryPool *ToArrowPool(const std::shared_ptr<cylon::CylonContext> &) { return arrow::default_memory_pool(); }
-// referenced only by the range-partition kernel (DistributedSort), which the checker never runs
-int CylonContext::GetWorldSize() { return 1; }
+// The context without MPI (ctx/cylon_context.cpp pulls in the MPI communicator): same observable behaviour for the
+// members the table operators use.
+CylonContext::CylonContext(bool distributed) { this->is_distributed = distributed; }
+std::shared_ptr<CylonContext> CylonContext::Init() { return std::make_shared<CylonContext>(false); }
+int CylonContext::GetRank() { return is_distributed ? communicator->GetRank() : 0; }
+int CylonContext::GetWorldSize() { return is_distributed ? communicator->GetWorldSize() : 1; }
+std::vector<int> CylonContext::GetNeighbours(bool include_self) {
+  std::vector<int> out;
+  const int w = GetWorldSize(), me = GetRank();
+  for (int r = 0; r < w; r++)
+    if (include_self || r != me) out.push_back(r);
+  return out;
+}
+int32_t CylonContext::GetNextSequence() { return sequence_no++; }
+std::shared_ptr<net::Communicator> CylonContext::GetCommunicator() const { return communicator; }
+void CylonContext::setCommunicator(const std::shared_ptr<cylon::net::Communicator> &c) { communicator = c; }
+void CylonContext::setDistributed(bool d) { is_distributed = d; }
+bool CylonContext::IsDistributed() const { return is_distributed; }
+Status PipelineGroupBy(std::shared_ptr<Table> &, int32_t, const std::vector<std::pair<int32_t, compute::AggregationOpId>> &,
+                       std::shared_ptr<Table> &) {
+  return Status(Code::NotImplemented, "pipeline group-by is not part of the checker build");
+}
+namespace io {
+arrow::Result<std::shared_ptr<arrow::Table>> read_csv(std::shared_ptr<cylon::CylonContext> &, const std::string &,
+                                                      cylon::io::config::CSVReadOptions) {
+  return arrow::Status::NotImplemented("no CSV reader in the checker build");
+}
+}  // namespace io
+namespace util {
+std::string generate_uuid_v4() {
+  static std::atomic<uint64_t> n{0};
+  return "checker-" + std::to_string(n++);
+}
+}  // namespace util
 namespace tarrow {
 std::shared_ptr<cylon::DataType> ToCylonType(const std::shared_ptr<arrow::DataType> &) { return nullptr; }
+// arrow/arrow_types.cpp does not compile against Arrow 24 (DecimalType constructor). The table code only asks it whether
+// a schema is made of types Cylon handles; the checker builds tables from the fixed list in type_of() below.
+bool validateArrowTableTypes(const std::shared_ptr<arrow::Table> &) { return true; }
+std::shared_ptr<arrow::DataType> convertToArrowType(const std::shared_ptr<DataType> &, int32_t, int32_t, int32_t) { return nullptr; }
 }  // namespace tarrow
 namespace compute {
 cylon::Status MinMax(std::shared_ptr<cylon::CylonContext> &, const arrow::Datum &, const std::shared_ptr<cylon::DataType> &,
@@ -241,5 +291,267 @@ int ref_table_copy_col(const ref_table *t, int32_t c, void *data, int32_t *offse
   return 0;
 }
 void ref_table_free(ref_table *t) { delete t; }
+// name of column c (valid until the table is freed): the reference's prefixes ("l_", "sum_", "sum_sum_" ...)
+const char *ref_table_col_name(const ref_table *t, int32_t c) { return t->t->field(c)->name().c_str(); }
+int32_t ref_table_col_type(const ref_table *t, int32_t c) { return (int32_t)t->t->field(c)->type()->id(); }  // arrow::Type::type
+
+}  // extern "C"
+
+// ---- ranks as threads: an in-process Communicator/Channel so that the reference's Distributed* operators run here ------
+// What MPIChannel shows its callbacks (net/mpi/mpi_channel.cpp:70-205) is kept: per message receivedHeader(source, 0,
+// new int[h], h) then receivedData(source, buffer from the Allocator, length) -- also for 0-length buffers -- and for
+// the end marker receivedHeader(source, 1, nullptr, 0); sends complete in the order they were accepted, the finish
+// marker after all of them. Messages between two ranks on one edge stay in order.
+namespace {
+
+struct MemMsg {
+  bool fin = false;
+  std::vector<int> header;
+  std::vector<uint8_t> data;
+};
+
+struct MemHub {
+  std::mutex mu;
+  std::map<std::tuple<int, int, int>, std::deque<MemMsg>> queues;  // (edge, source, target)
+  std::condition_variable cv;
+  int world = 1, waiting = 0;
+  uint64_t generation = 0;
+  void barrier() {
+    std::unique_lock<std::mutex> lk(mu);
+    const uint64_t gen = generation;
+    if (++waiting == world) {
+      waiting = 0;
+      generation++;
+      cv.notify_all();
+    } else {
+      cv.wait(lk, [&] { return generation != gen; });
+    }
+  }
+};
+
+class MemChannel : public cylon::Channel {
+ public:
+  MemChannel(MemHub *hub, int rank) : hub_(hub), rank_(rank) {}
+  void init(int edge, const std::vector<int> &receives, const std::vector<int> &sendIds, cylon::ChannelReceiveCallback *rcv,
+            cylon::ChannelSendCallback *send, cylon::Allocator *alloc) override {
+    edge_ = edge;
+    sources_ = receives;
+    rcv_ = rcv;
+    send_ = send;
+    alloc_ = alloc;
+    for (int t : sendIds) out_[t];
+  }
+  // Sends follow MPIChannel's per-target state machine (net/mpi/mpi_channel.cpp:139-205), one transition per
+  // progressSends() call, with transfers that complete at once: data of a target goes out in the order it was accepted,
+  // the finish marker only when no data is waiting, and a completion is reported in the call AFTER the one that posted
+  // the message. AllToAll::sendFinishComplete relies on that pacing (it marks sends[target] finished, which is a different
+  // entry than the one that sent the marker whenever rank != 0).
+  int send(std::shared_ptr<cylon::TxRequest> r) override {
+    out_[r->target].waiting.push_back(r);
+    return 1;
+  }
+  int sendFin(std::shared_ptr<cylon::TxRequest> r) override {
+    auto &t = out_[r->target];
+    if (t.fin) return -1;
+    t.fin = r;
+    return 1;
+  }
+  void post(int target, const std::shared_ptr<cylon::TxRequest> &r, bool fin) {
+    MemMsg m;
+    m.fin = fin;
+    if (!fin) {
+      m.header.assign(r->header, r->header + r->headerLength);
+      const uint8_t *b = static_cast<const uint8_t *>(r->buffer);
+      if (r->length > 0) m.data.assign(b, b + r->length);
+    }
+    std::lock_guard<std::mutex> lk(hub_->mu);
+    hub_->queues[{edge_, rank_, target}].push_back(std::move(m));
+  }
+  void progressSends() override {
+    for (auto &kv : out_) {
+      auto &t = kv.second;
+      switch (t.state) {
+        case 0:  // idle
+          if (!t.waiting.empty()) {
+            t.current = t.waiting.front();
+            t.waiting.pop_front();
+            post(kv.first, t.current, false);
+            t.state = 1;
+          } else if (t.fin) {
+            post(kv.first, t.fin, true);
+            t.state = 2;
+          }
+          break;
+        case 1: {  // a data message is out: report it, post what comes next
+          auto done = t.current;
+          t.current = nullptr;
+          if (!t.waiting.empty()) {
+            t.current = t.waiting.front();
+            t.waiting.pop_front();
+            post(kv.first, t.current, false);
+            send_->sendComplete(done);
+          } else {
+            send_->sendComplete(done);
+            if (t.fin) {
+              post(kv.first, t.fin, true);
+              t.state = 2;
+            } else {
+              t.state = 0;
+            }
+          }
+          break;
+        }
+        case 2:  // the finish marker is out
+          send_->sendFinishComplete(t.fin);
+          t.state = 3;
+          break;
+        default: break;
+      }
+    }
+  }
+  void progressReceives() override {
+    for (int src : sources_) {
+      while (true) {
+        MemMsg m;
+        {
+          std::lock_guard<std::mutex> lk(hub_->mu);
+          auto &q = hub_->queues[{edge_, src, rank_}];
+          if (q.empty()) break;
+          m = std::move(q.front());
+          q.pop_front();
+        }
+        if (m.fin) {
+          rcv_->receivedHeader(src, 1, nullptr, 0);
+          continue;
+        }
+        int *h = nullptr;
+        if (!m.header.empty()) {
+          h = new int[m.header.size()];
+          std::memcpy(h, m.header.data(), m.header.size() * sizeof(int));
+        }
+        rcv_->receivedHeader(src, 0, h, (int)m.header.size());
+        std::shared_ptr<cylon::Buffer> buf;
+        alloc_->Allocate((int64_t)m.data.size(), &buf);
+        if (!m.data.empty()) std::memcpy(buf->GetByteBuffer(), m.data.data(), m.data.size());
+        rcv_->receivedData(src, buf, (int)m.data.size());
+      }
+    }
+  }
+  void close() override {}
+
+ private:
+  MemHub *hub_;
+  int rank_, edge_ = 0;
+  std::vector<int> sources_;
+  cylon::ChannelReceiveCallback *rcv_ = nullptr;
+  cylon::ChannelSendCallback *send_ = nullptr;
+  cylon::Allocator *alloc_ = nullptr;
+  struct Out {
+    std::deque<std::shared_ptr<cylon::TxRequest>> waiting;
+    std::shared_ptr<cylon::TxRequest> current, fin;
+    int state = 0;
+  };
+  std::map<int, Out> out_;
+};
+
+class MemCommunicator : public cylon::net::Communicator {
+ public:
+  MemCommunicator(MemHub *hub, int r) : hub_(hub) {
+    rank = r;
+    world_size = hub->world;
+  }
+  void Init(const std::shared_ptr<cylon::net::CommConfig> &) override {}
+  cylon::Channel *CreateChannel() override { return new MemChannel(hub_, rank); }
+  int GetRank() override { return rank; }
+  int GetWorldSize() override { return world_size; }
+  void Finalize() override {}
+  void Barrier() override { hub_->barrier(); }
+  cylon::net::CommType GetCommType() override { return cylon::net::CommType::MPI; }
+
+ private:
+  MemHub *hub_;
+};
+
+}  // namespace
+
+extern "C" {
+
+// One Distributed* operator of the reference on `world` ranks (threads). lcols / rcols: world x nlc / world x nrc column
+// descriptors, rank-major. op: 0 DistributedJoin(p1 = left keys, p2 = right keys, join_type, algorithm, prefixes l_/r_),
+// 1/2/3 DistributedUnion/Subtract/Intersect, 4 DistributedUnique(p1 = columns), 5 Shuffle(p1 = hash columns),
+// 6 DistributedHashGroupBy(p1 = index columns, p2 = (aggregate column, AggregationOpId) pairs flattened).
+// out: `world` result tables (ref_table_*), in rank order. Returns the first non-zero cylon::Code, or 0.
+int ref_dist_op(int32_t op, int32_t world, const ref_col_in *lcols, int32_t nlc, const ref_col_in *rcols, int32_t nrc, const int32_t *p1,
+                int32_t n1, const int32_t *p2, int32_t n2, int32_t join_type, int32_t algorithm, ref_table **out) {
+  MemHub hub;
+  hub.world = world;
+  std::vector<int> codes((size_t)world, 0);
+  std::vector<std::shared_ptr<arrow::Table>> results((size_t)world);
+  auto body = [&](int r) {
+    auto ctx = std::make_shared<cylon::CylonContext>(world > 1);
+    if (world > 1) ctx->setCommunicator(std::make_shared<MemCommunicator>(&hub, r));
+    std::shared_ptr<cylon::Table> left, right, res;
+    auto lt = make_table(lcols + (size_t)r * nlc, nlc);
+    if (!lt || !cylon::Table::FromArrowTable(ctx, lt, left).is_ok()) {
+      codes[r] = 42;
+      return;
+    }
+    if (nrc > 0) {
+      auto rt = make_table(rcols + (size_t)r * nrc, nrc);
+      if (!rt || !cylon::Table::FromArrowTable(ctx, rt, right).is_ok()) {
+        codes[r] = 42;
+        return;
+      }
+    }
+    cylon::Status st;
+    const std::vector<int> v1(p1, p1 + n1);
+    switch (op) {
+      case 0: {
+        cylon::join::config::JoinConfig cfg(static_cast<cylon::join::config::JoinType>(join_type), v1, std::vector<int>(p2, p2 + n2),
+                                            static_cast<cylon::join::config::JoinAlgorithm>(algorithm), "l_", "r_");
+        st = cylon::DistributedJoin(left, right, cfg, res);
+        break;
+      }
+      case 1: st = cylon::DistributedUnion(left, right, res); break;
+      case 2: st = cylon::DistributedSubtract(left, right, res); break;
+      case 3: st = cylon::DistributedIntersect(left, right, res); break;
+      case 4: st = cylon::DistributedUnique(left, v1, res); break;
+      case 5: st = cylon::Shuffle(left, v1, res); break;
+      case 6: {
+        std::vector<int32_t> agg_cols;
+        std::vector<cylon::compute::AggregationOpId> agg_ops;
+        for (int i = 0; i + 1 < n2; i += 2) {
+          agg_cols.push_back(p2[i]);
+          agg_ops.push_back(static_cast<cylon::compute::AggregationOpId>(p2[i + 1]));
+        }
+        st = cylon::DistributedHashGroupBy(left, std::vector<int32_t>(p1, p1 + n1), agg_cols, agg_ops, res);
+        break;
+      }
+      default: st = cylon::Status(cylon::Code::Invalid, "unknown op");
+    }
+    if (!st.is_ok()) {
+      fprintf(stderr, "ref_dist_op(rank %d): %s\n", r, st.get_msg().c_str());
+      codes[r] = st.get_code() ? st.get_code() : 42;
+      return;
+    }
+    auto comb = res->get_table()->CombineChunks();
+    if (!comb.ok()) {
+      codes[r] = 42;
+      return;
+    }
+    results[r] = comb.ValueOrDie();
+  };
+  if (world == 1) {
+    body(0);
+  } else {
+    std::vector<std::thread> threads;
+    for (int r = 0; r < world; r++) threads.emplace_back(body, r);
+    for (auto &t : threads) t.join();
+  }
+  for (int r = 0; r < world; r++)
+    if (codes[r]) return codes[r];
+  for (int r = 0; r < world; r++) out[r] = new ref_table{results[r]};
+  return 0;
+}
 
 }  // extern "C"

@@ -26,6 +26,14 @@ struct hash<arrow::util::string_view> {
 };
 }  // namespace std
 
+#include <arrow/type_fwd.h>
+namespace arrow {
+namespace internal {
+// Arrow 2 had this in arrow/type.h; every type the shuffle carries except NA has a validity bitmap.
+inline bool HasValidityBitmap(Type::type id) { return id != Type::NA; }
+}  // namespace internal
+}  // namespace arrow
+
 #define CYLON_SRC_CYLON_CTX_ARROW_MEMORY_POOL_UTILS_HPP_
 namespace cylon {
 class CylonContext;

@@ -100,3 +100,99 @@ def test_aggregate_matches_reference_kernels(kind, op):
     assert np.array_equal(got, exp)  # floating-point SUM too: same sequential order of additions as the reference
     if dt.kind == "f" and op == orc.MAX:
         assert exp[3] == np.finfo(dt).tiny
+
+
+# ---- the reference's Distributed* operators themselves, ranks as threads (oracle/ref_shim: in-process communicator) -----
+from tests.helpers import assert_same_rows  # noqa: E402
+
+_has_dist = pyref.available() and hasattr(pyref.lib(), "ref_dist_op")
+dist = pytest.mark.skipif(not _has_dist, reason="oracle/_ref/libcylon_ref.so was built without the table operators")
+
+
+def _kv_tables(world, n, seed, dom, two_keys=False):
+    out = []
+    for r in range(world):
+        rng = np.random.default_rng(seed * 100 + r)
+        cols = [orc.col(rng.integers(-dom, dom, n + 3 * r).astype(np.int64), name="c0")]
+        if two_keys:
+            cols.append(orc.col(rng.integers(0, 4, n + 3 * r).astype(np.int32), name="c1"))
+        cols.append(orc.col(rng.integers(0, 1000, n + 3 * r).astype(np.float64) / 8, name="c%d" % len(cols)))
+        out.append(cols)
+    return out
+
+
+@dist
+@pytest.mark.parametrize("world", [1, 2, 3, 4])
+@pytest.mark.parametrize("jt", [orc.INNER, orc.LEFT, orc.RIGHT, orc.FULL_OUTER])
+@pytest.mark.parametrize("algo", [orc.SORT, orc.HASH])
+@pytest.mark.parametrize("two_keys", [False, True])
+def test_distributed_join_matches_reference_ranks(world, jt, algo, two_keys):
+    """cylon::DistributedJoin (table.cpp:482-502) run by the reference itself on `world` ranks: hash partition of both
+    tables on the key columns, the Arrow all-to-all, then the local join -- per-rank results as row multisets."""
+    lefts = _kv_tables(world, 60, 1, 40, two_keys)
+    rights = _kv_tables(world, 50, 2, 40, two_keys)
+    keys = [0, 1] if two_keys else [0]
+    exp = orc.distributed_join(lefts, rights, keys, keys, jt, algo, "l_", "r_")
+    got = pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=keys, p2=keys, join_type=jt, algorithm=algo)
+    for r in range(world):
+        assert [c.name for c in got[r]] == [c.name for c in exp[r]]
+        assert_same_rows(got[r], exp[r], "rank %d" % r)
+
+
+@dist
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("op,ref_op", [(orc.UNION, pyref.DIST_UNION), (orc.SUBTRACT, pyref.DIST_SUBTRACT), (orc.INTERSECT, pyref.DIST_INTERSECT)])
+def test_distributed_set_ops_match_reference_ranks(world, op, ref_op):
+    """DistributedUnion/Subtract/Intersect (table.cpp:727-785): shuffle on ALL columns, then the local set operator.
+    Numeric columns only -- the reference's cross-table string comparator is broken."""
+    lefts = _kv_tables(world, 80, 3, 6)   # small domains: many duplicate rows inside and across tables
+    rights = _kv_tables(world, 70, 3, 6)  # same seed family: overlaps with the left tables
+    for t in lefts + rights:
+        t[1].data[:] = np.floor(t[1].data) % 3
+    exp = orc.distributed_set_op(lefts, rights, op)
+    got = pyref.dist_op(ref_op, lefts, rights)
+    for r in range(world):
+        assert_same_rows(got[r], exp[r], "rank %d" % r)
+
+
+@dist
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("cols", [[0], [0, 1]])
+def test_distributed_unique_matches_reference_ranks(world, cols):
+    tables = _kv_tables(world, 90, 5, 8)
+    for t in tables:
+        t[1].data[:] = np.floor(t[1].data) % 2
+    exp = orc.distributed_unique(tables, cols)
+    got = pyref.dist_op(pyref.DIST_UNIQUE, tables, p1=cols)
+    for r in range(world):
+        if cols == [0, 1]:
+            assert_same_rows(got[r], exp[r], "rank %d" % r)
+        else:  # which duplicate survives depends on arrival order after the shuffle: compare the distinct keys
+            assert sorted(got[r][0].data.tolist()) == sorted(exp[r][0].data.tolist())
+
+
+@dist
+@pytest.mark.parametrize("world", [2, 3, 4])
+def test_shuffle_matches_reference_ranks(world):
+    tables = _kv_tables(world, 100, 7, 1000)
+    exp = orc.shuffle(tables, [0])
+    got = pyref.dist_op(pyref.DIST_SHUFFLE, tables, p1=[0])
+    assert sum(t[0].length for t in got) == sum(t[0].length for t in tables)  # cpp/test/table_op_test.cpp:38-47
+    for r in range(world):
+        assert_same_rows(got[r], exp[r], "rank %d" % r)
+
+
+@dist
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("ops", [[orc.SUM, orc.MIN, orc.MAX], [orc.SUM, orc.COUNT, orc.MIN, orc.MAX], [orc.COUNT]])
+def test_distributed_groupby_matches_reference_ranks(world, ops):
+    """DistributedHashGroupBy (groupby/groupby.cpp:33-83): column names (the doubled prefix after two associative
+    rounds), group placement by key hash, and the aggregate values. Values are multiples of 1/8 so sums are exact."""
+    tables = _kv_tables(world, 120, 9, 10)
+    for t in tables:
+        t[1].data[:] -= 60.0  # negative groups exist: MAX starts from DBL_MIN (G3)
+    exp = orc.distributed_hash_groupby(tables, [0], [1] * len(ops), ops)
+    got = pyref.dist_op(pyref.DIST_GROUPBY, tables, p1=[0], p2=[x for op in ops for x in (1, op)])
+    for r in range(world):
+        assert [c.name for c in got[r]] == [c.name for c in exp[r]]
+        assert_same_rows(got[r], exp[r], "rank %d" % r)
