@@ -172,9 +172,40 @@ def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return 0
     import multiprocessing as mp
+    from oracle import pyoracle as orc
     from oracle import pyref
     cores = os.cpu_count() or 1
     rows = args.ref_rows
+    if pyref.dist_available():
+        # The reference's own cylon::DistributedJoin (table.cpp:482-502: hash partition, split, Arrow all-to-all, local
+        # hash join) with one rank per host core. Ranks are threads of one process and the all-to-all goes through an
+        # in-memory channel instead of MPI (oracle/ref_shim), which can only flatter the reference.
+        lefts, rights = [], []
+        for r in range(cores):
+            lk, lv = synth_table(rows, rows * cores, 1, r)
+            rk, rv = synth_table(rows, rows * cores, 2, r)
+            lefts.append([orc.col(lk), orc.col(lv)])
+            rights.append([orc.col(rk), orc.col(rv)])
+        times, out_rows = [], 0
+        for step in range(args.warmup + args.steps):
+            per_rank, seconds = pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0], p2=[0], join_type=orc.INNER, algorithm=orc.HASH,
+                                              rows_only=True)
+            out_rows = sum(per_rank)
+            if step >= args.warmup:
+                times.append(seconds)
+        ms = 1e3 * float(np.mean(times))
+        value = 2.0 * rows * cores / (ms / 1e3)
+        sample = ("cylon::DistributedJoin of the reference, %d ranks (threads, in-memory all-to-all) x (%d x %d rows), %d output rows "
+                  "per step, whole operator timed" % (cores, rows, rows, out_rows))
+        line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "int64", "data": "synthetic",
+                "config": {"workload": "DistributedJoin inner hash join, int64 key + double payload, uniform keys in [0, rows*ranks); CPU "
+                                       "sample of %d rows per side per rank, %d ranks (one per host core)" % (rows, cores)},
+                "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+                "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
     times = []
     with mp.get_context("fork").Pool(cores) as pool:
         for step in range(args.warmup + args.steps):

@@ -4,6 +4,7 @@ ONLY -- it pins the oracle (tests/test_oracle_vs_reference.py) and serves as the
 """
 import ctypes as C
 import os
+import time
 
 import numpy as np
 
@@ -146,7 +147,7 @@ def _table_out(h):
 DIST_JOIN, DIST_UNION, DIST_SUBTRACT, DIST_INTERSECT, DIST_UNIQUE, DIST_SHUFFLE, DIST_GROUPBY = range(7)
 
 
-def dist_op(op, lefts, rights=None, p1=(), p2=(), join_type=0, algorithm=0):
+def dist_op(op, lefts, rights=None, p1=(), p2=(), join_type=0, algorithm=0, rows_only=False):
     """One Distributed* operator of the reference on len(lefts) ranks (threads inside this process, an in-memory
     Communicator/Channel in place of MPI). lefts / rights: one oracle-style table per rank. -> one table per rank."""
     world = len(lefts)
@@ -160,11 +161,24 @@ def dist_op(op, lefts, rights=None, p1=(), p2=(), join_type=0, algorithm=0):
     a1 = (C.c_int32 * max(1, len(p1)))(*p1)
     a2 = (C.c_int32 * max(1, len(p2)))(*p2)
     outs = (C.c_void_p * world)()
+    t0 = time.perf_counter()
     rc = lib().ref_dist_op(C.c_int32(op), C.c_int32(world), la, C.c_int32(nlc), ra, C.c_int32(nrc), a1, C.c_int32(len(p1)), a2,
                            C.c_int32(len(p2)), C.c_int32(join_type), C.c_int32(algorithm), outs)
+    seconds = time.perf_counter() - t0
     if rc != 0:
         raise RuntimeError("reference operator failed with cylon::Code %d" % rc)
+    if rows_only:  # benchmark use: (rows per rank, seconds inside the reference call), results not copied out
+        rows = []
+        for r in range(world):
+            h = C.c_void_p(outs[r])
+            rows.append(lib().ref_table_rows(h))
+            lib().ref_table_free(h)
+        return rows, seconds
     return [_table_out(C.c_void_p(outs[r])) for r in range(world)]
+
+
+def dist_available():
+    return available() and hasattr(lib(), "ref_dist_op")
 
 
 # ---- the reference's aggregation kernels (compute/aggregate_kernels.hpp, compiled by oracle/build_ref.sh) ------------
