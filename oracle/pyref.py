@@ -28,7 +28,8 @@ def lib():
 
 
 class RefColIn(C.Structure):
-    _fields_ = [("type", C.c_int32), ("width", C.c_int32), ("n", C.c_int64), ("offsets", C.c_void_p), ("data", C.c_void_p)]
+    _fields_ = [("type", C.c_int32), ("width", C.c_int32), ("n", C.c_int64), ("offsets", C.c_void_p), ("data", C.c_void_p),
+                ("validity", C.c_void_p)]
 
 
 def _args(col):
@@ -82,6 +83,11 @@ def _table_in(cols):
         arr[i].type, arr[i].width, arr[i].n = c.type, c.byte_width, c.length
         arr[i].offsets = c.offsets.ctypes.data if c.offsets is not None else None
         arr[i].data = data.ctypes.data
+        arr[i].validity = None
+        if c.validity is not None:
+            v = np.ascontiguousarray(c.validity, dtype=np.uint8)
+            keep.append(v)
+            arr[i].validity = v.ctypes.data
     return arr, keep
 
 

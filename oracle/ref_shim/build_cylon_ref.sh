@@ -14,7 +14,7 @@ LIBARROW=$(ls "$PA_LIB"/libarrow.so.* | head -1)
 LIBARROW_COMPUTE=$(ls "$PA_LIB"/libarrow_compute.so.* | head -1)
 SRCS="$REF/join/join.cpp $REF/join/hash_join.cpp $REF/join/sort_join.cpp $REF/join/join_utils.cpp \
       $REF/arrow/arrow_partition_kernels.cpp $REF/arrow/arrow_comparator.cpp $REF/util/arrow_utils.cpp $REF/arrow/arrow_kernels.cpp \
-      $REF/util/murmur3.cpp \
+      $REF/util/murmur3.cpp $REF/util/copy_arrray.cpp \
       $REF/table.cpp $REF/table_api.cpp $REF/column.cpp $REF/row.cpp $REF/indexing/index.cpp $REF/partition/partition.cpp \
       $REF/groupby/groupby.cpp $REF/groupby/hash_groupby.cpp $REF/arrow/arrow_all_to_all.cpp $REF/net/ops/all_to_all.cpp \
       $REF/net/TxRequest.cpp $REF/util/builtins.cpp $REF/io/csv_read_config.cpp $REF/io/csv_write_config.cpp"

@@ -40,25 +40,6 @@ cylon::Status AllReduce(const void *, void *, int, const std::shared_ptr<DataTyp
   return cylon::Status(cylon::Code::NotImplemented, "no MPI in the checker build");
 }
 }  // namespace mpi
-namespace util {
-// util/copy_arrray.cpp does not compile against Arrow 24 (NumericBuilder<BooleanType> no longer exists), so the
-// checker supplies the one function the join code needs from it, with the documented semantics
-// (util/copy_arrray.cpp:24-110: index -1 -> null, otherwise the value) expressed through arrow::compute::Take.
-// The join algorithms themselves (hash_join.cpp, sort_join.cpp, join_utils.cpp) are the reference's own code.
-arrow::Status copy_array_by_indices(const std::vector<int64_t> &indices, const std::shared_ptr<arrow::Array> &data_array,
-                                    std::shared_ptr<arrow::Array> *copied_array, arrow::MemoryPool *memory_pool) {
-  arrow::Int64Builder b(memory_pool);
-  ARROW_RETURN_NOT_OK(b.Reserve((int64_t)indices.size()));
-  for (int64_t v : indices) {
-    if (v < 0) b.UnsafeAppendNull(); else b.UnsafeAppend(v);
-  }
-  std::shared_ptr<arrow::Array> idx;
-  ARROW_RETURN_NOT_OK(b.Finish(&idx));
-  ARROW_ASSIGN_OR_RAISE(auto taken, arrow::compute::Take(arrow::Datum(data_array), arrow::Datum(idx)));
-  *copied_array = taken.make_array();
-  return arrow::Status::OK();
-}
-}  // namespace util
 arrow::MemoryPool *ToArrowPool(const std::shared_ptr<cylon::CylonContext> &) { return arrow::default_memory_pool(); }
 // The context without MPI (ctx/cylon_context.cpp pulls in the MPI communicator): same observable behaviour for the
 // members the table operators use.
@@ -205,11 +186,13 @@ struct ref_col_in {
   int64_t n;
   const int32_t *offsets;
   const void *data;
+  const uint8_t *validity;  // Arrow validity bitmap (LSB first) or NULL = no nulls
 };
 
 // The reference's single-key SORT join sorts the key column IN PLACE, so tables handed to it own
 // mutable copies of the caller's buffers.
-static std::shared_ptr<arrow::Array> own(int32_t type, int32_t width, int64_t n, const int32_t *offsets, const void *data) {
+static std::shared_ptr<arrow::Array> own(int32_t type, int32_t width, int64_t n, const int32_t *offsets, const void *data,
+                                         const uint8_t *validity = nullptr) {
   auto dt = type_of(type);
   if (!dt) return nullptr;
   auto copy = [](const void *p, int64_t bytes) -> std::shared_ptr<arrow::Buffer> {
@@ -220,21 +203,21 @@ static std::shared_ptr<arrow::Array> own(int32_t type, int32_t width, int64_t n,
     return b;
   };
   std::vector<std::shared_ptr<arrow::Buffer>> bufs;
-  bufs.push_back(nullptr);
+  bufs.push_back(validity ? copy(validity, (n + 7) / 8) : nullptr);
   if (type == 13 || type == 14) {
     bufs.push_back(copy(offsets, (n + 1) * 4));
     bufs.push_back(copy(data, n > 0 ? (int64_t)offsets[n] : 0));
   } else {
     bufs.push_back(copy(data, n * (int64_t)width));
   }
-  return arrow::MakeArray(arrow::ArrayData::Make(dt, n, bufs, 0));
+  return arrow::MakeArray(arrow::ArrayData::Make(dt, n, bufs, validity ? arrow::kUnknownNullCount : 0));
 }
 
 static std::shared_ptr<arrow::Table> make_table(const ref_col_in *cols, int32_t ncols) {
   std::vector<std::shared_ptr<arrow::Field>> fields;
   std::vector<std::shared_ptr<arrow::Array>> arrays;
   for (int c = 0; c < ncols; c++) {
-    auto a = own(cols[c].type, cols[c].width, cols[c].n, cols[c].offsets, cols[c].data);
+    auto a = own(cols[c].type, cols[c].width, cols[c].n, cols[c].offsets, cols[c].data, cols[c].validity);
     if (!a) return nullptr;
     fields.push_back(arrow::field("c" + std::to_string(c), a->type()));
     arrays.push_back(a);

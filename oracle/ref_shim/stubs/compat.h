@@ -34,6 +34,17 @@ inline bool HasValidityBitmap(Type::type id) { return id != Type::NA; }
 }  // namespace internal
 }  // namespace arrow
 
+#include <arrow/array/builder_primitive.h>
+namespace arrow {
+// util/copy_arrray.cpp:148 instantiates its numeric copy for BooleanType through NumericBuilder<BooleanType>, which
+// Arrow 2 accepted. This specialisation only lets that one instantiation compile; the checker never builds BOOL columns.
+template <>
+class NumericBuilder<BooleanType> : public BooleanBuilder {
+ public:
+  using BooleanBuilder::BooleanBuilder;
+};
+}  // namespace arrow
+
 #define CYLON_SRC_CYLON_CTX_ARROW_MEMORY_POOL_UTILS_HPP_
 namespace cylon {
 class CylonContext;

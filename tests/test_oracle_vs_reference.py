@@ -196,3 +196,51 @@ def test_distributed_groupby_matches_reference_ranks(world, ops):
     for r in range(world):
         assert [c.name for c in got[r]] == [c.name for c in exp[r]]
         assert_same_rows(got[r], exp[r], "rank %d" % r)
+
+
+# ---- null inputs: what the reference really does with them (no reference test covers this; the compiled reference does) --
+def _with_nulls(tables, seed):
+    for r, t in enumerate(tables):
+        rng = np.random.default_rng(seed * 31 + r)
+        for c in t:
+            c.validity = np.packbits(rng.random(c.length) >= 0.2, bitorder="little")
+    return tables
+
+
+@dist
+@pytest.mark.parametrize("world", [1, 2, 3])
+@pytest.mark.parametrize("jt", [orc.INNER, orc.LEFT, orc.RIGHT, orc.FULL_OUTER])
+@pytest.mark.parametrize("algo", [orc.SORT, orc.HASH])
+def test_join_with_null_inputs_matches_reference(world, jt, algo):
+    """Keys under a null bit still hash, partition and compare by their value slot (A6); the gather does not carry source
+    validity (copy_arrray.cpp:24-50), only the -1 fill makes nulls; after a shuffle every input null bit is gone (B2)."""
+    lefts, rights = _with_nulls(_kv_tables(world, 60, 11, 20), 1), _with_nulls(_kv_tables(world, 50, 12, 20), 2)
+    exp = orc.distributed_join(lefts, rights, [0], [0], jt, algo, "l_", "r_")
+    got = pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0], p2=[0], join_type=jt, algorithm=algo)
+    for r in range(world):
+        assert_same_rows(got[r], exp[r], "rank %d" % r)
+
+
+@dist
+@pytest.mark.parametrize("world", [1, 2])
+def test_set_ops_unique_groupby_shuffle_with_null_inputs_match_reference(world):
+    lefts, rights = _with_nulls(_kv_tables(world, 80, 13, 6), 3), _with_nulls(_kv_tables(world, 70, 13, 6), 4)
+    for t in lefts + rights:
+        t[1].data[:] = np.floor(t[1].data) % 3
+    for op, ref_op in ((orc.UNION, pyref.DIST_UNION), (orc.SUBTRACT, pyref.DIST_SUBTRACT), (orc.INTERSECT, pyref.DIST_INTERSECT)):
+        exp, got = orc.distributed_set_op(lefts, rights, op), pyref.dist_op(ref_op, lefts, rights)
+        for r in range(world):
+            assert_same_rows(got[r], exp[r], "set op %d rank %d" % (op, r))
+    exp, got = orc.distributed_unique(lefts, [0, 1]), pyref.dist_op(pyref.DIST_UNIQUE, lefts, p1=[0, 1])
+    for r in range(world):
+        assert_same_rows(got[r], exp[r], "unique rank %d" % r)
+    ops = [orc.SUM, orc.COUNT, orc.MIN, orc.MAX]  # COUNT counts rows under a null bit too (G3)
+    exp = orc.distributed_hash_groupby(lefts, [0], [1] * 4, ops)
+    got = pyref.dist_op(pyref.DIST_GROUPBY, lefts, p1=[0], p2=[x for o in ops for x in (1, o)])
+    for r in range(world):
+        assert_same_rows(got[r], exp[r], "group-by rank %d" % r)
+    if world > 1:
+        exp, got = orc.shuffle(lefts, [0]), pyref.dist_op(pyref.DIST_SHUFFLE, lefts, p1=[0])
+        for r in range(world):
+            assert all(c.validity is None for c in got[r])  # B2: Split appends values only
+            assert_same_rows(got[r], exp[r], "shuffle rank %d" % r)
