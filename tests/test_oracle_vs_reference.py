@@ -244,3 +244,33 @@ def test_set_ops_unique_groupby_shuffle_with_null_inputs_match_reference(world):
         for r in range(world):
             assert all(c.validity is None for c in got[r])  # B2: Split appends values only
             assert_same_rows(got[r], exp[r], "shuffle rank %d" % r)
+
+
+@dist
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_string_payload_through_join_and_shuffle_matches_reference(world):
+    """Strings as PAYLOAD are safe in the reference (only cross-table string comparisons are broken, E3): the string
+    splitter (arrow_kernels.cpp:115-157), the all-to-all of offset + data buffers and the binary gather
+    (copy_arrray.cpp:52-85), including empty strings."""
+    words = ["", "a", "bb", "cylon", "hash-partition", "x" * 40]
+
+    def tables(seed):
+        out = []
+        for r in range(world):
+            rng = np.random.default_rng(seed * 10 + r)
+            n = 70 + 5 * r
+            out.append([orc.col(rng.integers(0, 25, n).astype(np.int64), name="c0"),
+                        orc.col([words[i] for i in rng.integers(0, len(words), n)], name="c1"),
+                        orc.col(rng.integers(0, 100, n).astype(np.float64), name="c2")])
+        return out
+
+    lefts, rights = tables(1), tables(2)
+    for jt in (orc.INNER, orc.FULL_OUTER):
+        exp = orc.distributed_join(lefts, rights, [0], [0], jt, orc.HASH, "l_", "r_")
+        got = pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0], p2=[0], join_type=jt, algorithm=orc.HASH)
+        for r in range(world):
+            assert_same_rows(got[r], exp[r], "join %d rank %d" % (jt, r))
+    if world > 1:
+        exp, got = orc.shuffle(lefts, [0]), pyref.dist_op(pyref.DIST_SHUFFLE, lefts, p1=[0])
+        for r in range(world):
+            assert_same_rows(got[r], exp[r], "shuffle rank %d" % r)
