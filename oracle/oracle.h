@@ -5,13 +5,18 @@
  * legs may build, load or call this. The product (cylon_b200/) never links or calls it.
  *
  * Every function follows the cited reference code (paths relative to
- * /root/reference/cpp/src/cylon/). All pointers are HOST pointers. Parity status:
- * pinned by the reference's own golden files and known-answer vectors (tests/golden/,
- * tests/test_oracle_golden.py) for: murmur3, int/double/string row hashing, partition ids,
- * INNER hash/sort join per rank at world 1/2/4, 2-column-key join, union/subtract/intersect
- * per rank, unique, groupby totals. LEFT/RIGHT/FULL_OUTER joins, string columns in set
- * operations, MIN/MAX group-by and null inputs are "parity unpinned" (no reference test or
- * golden covers them); there the oracle is a line-by-line restatement of the cited code.
+ * /root/reference/cpp/src/cylon/). All pointers are HOST pointers. Parity status: PINNED,
+ * two ways. (1) The reference's own golden files and known-answer vectors (tests/golden/,
+ * tests/test_oracle_golden.py): murmur3, int/double/string row hashing, partition ids, INNER
+ * hash/sort join per rank at world 1/2/4, 2-column-key join, union/subtract/intersect per rank,
+ * unique, groupby totals. (2) The reference's own code compiled in place and run as the checker
+ * (oracle/_ref/libcylon_ref.so, oracle/ref_shim/, tests/test_oracle_vs_reference.py): its
+ * DistributedJoin (all four types, hash and sort, one- and two-column keys), DistributedUnion/
+ * Subtract/Intersect, DistributedUnique, Shuffle and DistributedHashGroupBy on 1-4 ranks
+ * (threads + an in-memory channel in place of MPI), its aggregation kernels, and null inputs.
+ * Still "parity unpinned": string columns in set operations and string join keys -- the
+ * reference's cross-table string comparator is broken, so there the oracle
+ * restates the intended semantics of the cited code.
  */
 #ifndef CYLON_ORACLE_H_
 #define CYLON_ORACLE_H_
