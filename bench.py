@@ -360,16 +360,23 @@ def main():
         else:
             got = [0] * len(lanes)
 
+            errors = []
+
             def lane_main(li):
-                torch.cuda.set_device(local_rank)  # the CUDA current device is per host thread
-                for sidx in range(li, args.steps, len(lanes)):
-                    got[li] = e2e_step(*lanes[li])
+                try:
+                    torch.cuda.set_device(local_rank)  # the CUDA current device is per host thread
+                    for sidx in range(li, args.steps, len(lanes)):
+                        got[li] = e2e_step(*lanes[li])
+                except BaseException as exc:  # a failed lane must fail the run, not vanish with its thread
+                    errors.append(exc)
 
             threads = [threading.Thread(target=lane_main, args=(li,)) for li in range(len(lanes))]
             for th in threads:
                 th.start()
             for th in threads:
                 th.join()
+            if errors:
+                raise errors[0]
             torch.cuda.synchronize()
             wall_ms = 1e3 * (time.perf_counter() - t0)  # host clock around all K steps: spans both streams
             mm = got[0]
