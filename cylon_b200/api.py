@@ -130,6 +130,64 @@ class Table:
         return cls(h, ctx)
 
     @classmethod
+    def from_arrow(cls, ctx, arrow_table):
+        """Table::FromArrowTable (table.cpp:202-211) for a pyarrow.Table in host memory: every column's Arrow buffers
+        (validity, offsets, data) go to HBM as they are -- numeric, date/time/timestamp, string and binary columns;
+        chunked columns are combined first. Anything else raises CylonError(Code::NotImplemented)."""
+        import pyarrow as pa
+
+        t = arrow_table.combine_chunks()
+        columns, types, validity, names = [], [], [], []
+        for name, chunked in zip(t.column_names, t.columns):
+            arr = chunked.chunk(0) if chunked.num_chunks else pa.array([], type=chunked.type)
+            tid, n, off = arr.type.id, len(arr), arr.offset
+            bufs = arr.buffers()
+            if tid in capi.TYPE2NP:
+                dt = capi.TYPE2NP[tid]
+                data = np.frombuffer(bufs[1], dtype=dt)[off:off + n] if n else np.zeros(0, dtype=dt)
+                columns.append(data)
+            elif tid in (STRING, BINARY):
+                offs = np.frombuffer(bufs[1], dtype=np.int32)[off:off + n + 1] if n else np.zeros(1, dtype=np.int32)
+                data = np.frombuffer(bufs[2], dtype=np.uint8) if bufs[2] is not None and bufs[2].size else np.zeros(0, dtype=np.uint8)
+                columns.append((offs, data))
+            else:
+                raise capi.CylonError(10, "from_arrow: column %r has unsupported Arrow type %s" % (name, arr.type))
+            v = None
+            if arr.null_count:
+                v = np.unpackbits(np.frombuffer(bufs[0], dtype=np.uint8), bitorder="little")[off:off + n].astype(bool)
+            types.append(tid)
+            validity.append(v)
+            names.append(name)
+        return cls.from_numpy(ctx, columns, names=names, types=types, validity=validity)
+
+    def to_arrow(self):
+        """Table::ToArrowTable (table.cpp:477-480): a pyarrow.Table in host memory with the same column names, types
+        (by arrow::Type id) and nulls."""
+        import pyarrow as pa
+
+        by_id = {capi.UINT8: pa.uint8(), capi.INT8: pa.int8(), capi.UINT16: pa.uint16(), capi.INT16: pa.int16(), capi.UINT32: pa.uint32(),
+                 capi.INT32: pa.int32(), capi.UINT64: pa.uint64(), capi.INT64: pa.int64(), FLOAT: pa.float32(), DOUBLE: pa.float64(),
+                 STRING: pa.string(), BINARY: pa.binary(),
+                 capi.DATE32: pa.date32(), capi.DATE64: pa.date64(), capi.TIMESTAMP: pa.timestamp("us"), capi.TIME32: pa.time32("ms"),
+                 capi.TIME64: pa.time64("us")}
+        arrays, names = [], []
+        for c in self.to_host():
+            if c["type"] not in by_id:
+                raise capi.CylonError(10, "to_arrow: column %r has a type without an Arrow mapping here (%d)" % (c["name"], c["type"]))
+            n = len(c["offsets"]) - 1 if c["offsets"] is not None else len(c["data"])
+            vbuf, nulls = None, 0
+            if c["valid"] is not None:
+                nulls = int(n - np.count_nonzero(c["valid"]))
+                vbuf = pa.py_buffer(np.packbits(c["valid"], bitorder="little").tobytes())
+            if c["type"] in (STRING, BINARY):
+                bufs = [vbuf, pa.py_buffer(c["offsets"].tobytes()), pa.py_buffer(c["data"].tobytes())]
+            else:
+                bufs = [vbuf, pa.py_buffer(np.ascontiguousarray(c["data"]).tobytes())]
+            arrays.append(pa.Array.from_buffers(by_id[c["type"]], n, bufs, null_count=nulls))
+            names.append(c["name"])
+        return pa.Table.from_arrays(arrays, names=names)
+
+    @classmethod
     def from_device(cls, ctx, dcols, names=None):
         """Zero-copy view over capi.DCol device columns (they must outlive the table)."""
         n = len(dcols)
