@@ -15,7 +15,15 @@ _lib = None
 
 
 def available():
-    return os.path.exists(_PATH)
+    """True when the compiled reference exists AND loads here (it links pyarrow's libarrow by rpath; on a machine where
+    that path differs the tests that need it skip instead of erroring)."""
+    if not os.path.exists(_PATH):
+        return False
+    try:
+        lib()
+        return True
+    except OSError:
+        return False
 
 
 def lib():
@@ -194,7 +202,13 @@ _AGG_DTYPES = {"int8": 0, "int16": 1, "int32": 2, "int64": 3, "uint8": 4, "uint1
 
 
 def aggregate_available():
-    return os.path.exists(_AGG_PATH)
+    if not os.path.exists(_AGG_PATH):
+        return False
+    try:
+        C.CDLL(_AGG_PATH)
+        return True
+    except OSError:
+        return False
 
 
 def ref_aggregate(op, values, gid, num_groups):
