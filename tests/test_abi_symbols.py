@@ -32,3 +32,19 @@ def test_version_and_error_string_without_gpu():
     assert lib.cyl_version() >= 100
     lib.cyl_last_error.restype = ctypes.c_char_p
     assert isinstance(lib.cyl_last_error(), bytes)
+
+
+def test_cpp_operator_api_compiles_and_links_like_reference_user_code(tmp_path):
+    """tests/cpp/api_surface.cpp calls every operator of SURVEY.md 8(b) with the reference's names, argument order and
+    JoinConfig factories; it must compile against include/cylon/ (no CUDA headers needed) and link with the library."""
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    so_dir = os.path.join(root, "cylon_b200", "lib")
+    if shutil.which("g++") is None or not os.path.exists(os.path.join(so_dir, "libcylon_b200.so")):
+        pytest.skip("needs g++ and the built library")
+    exe = str(tmp_path / "api_surface")
+    r = subprocess.run(["g++", "-std=c++17", "-I" + os.path.join(root, "include"), os.path.join(root, "tests", "cpp", "api_surface.cpp"),
+                        "-o", exe, "-L" + so_dir, "-lcylon_b200", "-Wl,-rpath," + so_dir], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert subprocess.run([exe]).returncode == 0  # loads the library, returns before any GPU call
