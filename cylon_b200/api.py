@@ -43,6 +43,10 @@ class CylonContext:
         check(lib().cylon_context_set_stream(self._h, C.c_void_p(cuda_stream)))
         self._stream = cuda_stream
 
+    def add_config(self, key, value):
+        """CylonContext::AddConfig; see include/cylon_b200_api.h for the keys this library reads."""
+        check(lib().cylon_context_add_config(self._h, str(key).encode(), str(value).encode()))
+
     def get_rank(self):
         return lib().cylon_context_rank(self._h)
 

@@ -71,6 +71,18 @@ struct Scratch {
 };
 
 int num_sms();
+// "once per device" latch for per-(function, device) settings such as cudaFuncSetAttribute: first() is true the first
+// time it is asked with a given device current (a per-process flag would leave a second device of the process unset).
+struct PerDeviceOnce {
+  bool done[64] = {false};
+  bool first() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+    if (done[dev]) return false;
+    done[dev] = true;
+    return true;
+  }
+};
 static inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int64_t next_pow2(int64_t n) {
   int64_t c = 1;
@@ -249,8 +261,13 @@ __device__ __forceinline__ uint32_t ref_partition_of(uint32_t h, uint32_t p, boo
 }
 
 // 64 bits describing one value for the library's own hash containers (NOT the reference hash):
-// exact bits for fixed width <= 8, two-seed murmur otherwise. -0.0 is folded onto +0.0 so that values that
-// compare equal get equal bits.
+// exact bits for fixed width <= 8, two-seed murmur otherwise.
+//
+// Identity of floating-point keys is their BIT PATTERN, as it is in the reference: it hashes the bits (murmur3,
+// arrow_partition_kernels.cpp:138-143) and its containers only ever compare keys that hashed alike, so -0.0 and +0.0
+// are two keys and NaNs with identical bits are one key in Union/Unique/GroupBy and multi-column joins (run against
+// the compiled reference in tests/test_gpu_float_keys.py). The one exception is the single-key join, whose reference
+// comparator is operator== (arrow_comparator.cpp:240-243): there a NaN key matches nothing (key_bits_is_nan below).
 __device__ inline uint64_t value_bits64(const DCol &c, int64_t i) {
   if (c.kind == HK_MURMUR_VAR) {
     const int32_t b = c.offsets[i], e = c.offsets[i + 1];
@@ -260,10 +277,14 @@ __device__ inline uint64_t value_bits64(const DCol &c, int64_t i) {
     const uint8_t *p = c.data + i * (int64_t)c.width;
     return ((uint64_t)murmur3_32(p, c.width, 0x9747b28cu) << 32) | murmur3_32(p, c.width, 0);
   }
-  uint64_t v = load_bits(c, i);
-  if (c.type == CYL_DOUBLE && v == 0x8000000000000000ULL) v = 0;
-  if (c.type == CYL_FLOAT && v == 0x80000000ULL) v = 0;
-  return v;
+  return load_bits(c, i);
+}
+
+// NaN test on the raw bits of a FLOAT / DOUBLE key (false for every other type)
+__host__ __device__ __forceinline__ bool key_bits_is_nan(int32_t type, uint64_t bits) {
+  if (type == CYL_DOUBLE) return (bits & 0x7FFFFFFFFFFFFFFFULL) > 0x7FF0000000000000ULL;
+  if (type == CYL_FLOAT) return (bits & 0x7FFFFFFFULL) > 0x7F800000ULL;
+  return false;
 }
 
 // 64-bit tag of a row over the key columns. exact==true: one fixed-width column, tag == value bits.
@@ -274,8 +295,7 @@ __device__ inline uint64_t row_tag(const DCols &k, int64_t i, bool exact, uint64
   return h;
 }
 
-// value equality as the reference's comparators define it (arrow_comparator.cpp:107-130,205-281):
-// numeric by value (so NaN != NaN), binary by bytes+length.
+// value identity used to verify hashed candidates: numeric by bit pattern (see value_bits64), binary by bytes+length.
 __device__ inline bool value_equal(const DCol &a, int64_t i, const DCol &b, int64_t j) {
   if (a.kind == HK_MURMUR_VAR) {
     const int32_t ab = a.offsets[i], al = a.offsets[i + 1] - ab;
@@ -286,8 +306,6 @@ __device__ inline bool value_equal(const DCol &a, int64_t i, const DCol &b, int6
       if (p[t] != q[t]) return false;
     return true;
   }
-  if (a.type == CYL_DOUBLE) return reinterpret_cast<const double *>(a.data)[i] == reinterpret_cast<const double *>(b.data)[j];
-  if (a.type == CYL_FLOAT) return reinterpret_cast<const float *>(a.data)[i] == reinterpret_cast<const float *>(b.data)[j];
   if (a.width <= 8) return load_bits(a, i) == load_bits(b, j);
   const uint8_t *p = a.data + i * (int64_t)a.width, *q = b.data + j * (int64_t)b.width;
   for (int32_t t = 0; t < a.width; t++)

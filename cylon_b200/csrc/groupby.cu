@@ -196,6 +196,7 @@ int cyl_groupby_hash(const cyl_column_t *keys, int32_t nkeys, int64_t nrows, int
   CYL_TRY(make_dcols(keys, nkeys, nrows, &a.keys, "cyl_groupby_hash"));
   *num_groups = 0;
   if (nrows == 0) return CYL_OK;
+  if (nrows > (1ll << 30)) return fail(CYL_CapacityError, "cyl_groupby_hash: %lld rows (max 2^30 per GPU: 32-bit slot indices)", (long long)nrows);
   a.n = nrows;
   a.exact = is_exact_key(a.keys) ? 1 : 0;
   a.first = first_mask;

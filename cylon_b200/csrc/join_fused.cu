@@ -52,7 +52,7 @@ struct FusedArgs {
   unsigned int *work_counter;
 };
 
-// key bits as the join compares them: zero-extended raw bits, -0.0 folded onto +0.0 (value equality)
+// key bits as the join compares them: zero-extended raw bits (floating-point identity = bit pattern, see common.cuh)
 __device__ __forceinline__ uint64_t canon_key(const uint8_t *base, int64_t i, int32_t width, int32_t type) {
   uint64_t v;
   switch (width) {
@@ -61,8 +61,7 @@ __device__ __forceinline__ uint64_t canon_key(const uint8_t *base, int64_t i, in
     case 4: v = reinterpret_cast<const uint32_t *>(base)[i]; break;
     default: v = reinterpret_cast<const uint64_t *>(base)[i]; break;
   }
-  if (type == CYL_DOUBLE && v == 0x8000000000000000ULL) v = 0;
-  if (type == CYL_FLOAT && v == 0x80000000ULL) v = 0;
+  (void)type;
   return v;
 }
 
@@ -178,7 +177,10 @@ __global__ void __launch_bounds__(kFusedThreads) fused_join_kernel(const __grid_
         unsigned int cnt = 0;
         if (r < p1) {
           k = canon_key(a.p.src[a.p.key], r, pkw, a.p.key_type);
-          for (uint32_t j = heads[(uint32_t)mix64(k) & hmask]; j != kFusedNil; j = next[j]) {
+          // a NaN key joins nothing (operator== in the reference's single-key comparator); NaN build rows are linked but
+          // can only be reached by an identical NaN probe key, which stops here
+          uint32_t j = key_bits_is_nan(a.p.key_type, k) ? kFusedNil : heads[(uint32_t)mix64(k) & hmask];
+          for (; j != kFusedNil; j = next[j]) {
             if (canon_key(bkey_s, j, bkw, a.b.key_type) == k) {
               if (cnt == 0) first = j;
               cnt++;
@@ -225,8 +227,10 @@ static inline int grid1d(int64_t n, int per_block) {
   return (int)(b < 1 ? 1 : (b < cap ? b : cap));
 }
 
+// Validity bitmaps do not disqualify a column: the join's result carries no source validity (copy_arrray.cpp:39-47
+// appends the value slot of every matched row) and keys are hashed and compared by their value slot, so
+// an INNER join never reads a validity bit.
 static bool fused_type_ok(const cyl_column_t &c) {
-  if (c.validity != nullptr) return false;
   switch (c.type) {
     case CYL_UINT8: case CYL_INT8: return c.byte_width == 1;
     case CYL_UINT16: case CYL_INT16: return c.byte_width == 2;
@@ -412,10 +416,9 @@ int cyl_hash_join_fused_inner(const cyl_column_t *lcols, int32_t nlcols, int32_t
   a.out_cursor = counters.as<unsigned long long>();
   a.work_counter = reinterpret_cast<unsigned int *>(counters.as<char>() + 16);
 
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused_join_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-    attr_set = true;
   }
   int64_t grid = (int64_t)num_sms() * 2;
   if (grid > nbins) grid = nbins;

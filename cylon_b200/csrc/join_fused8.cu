@@ -31,7 +31,11 @@ struct F8PartArgs {
   uint64_t *rec;
 };
 
-__device__ __forceinline__ uint64_t f8_canon(uint64_t v, int key_is_f64) { return (key_is_f64 && v == 0x8000000000000000ULL) ? 0ull : v; }
+// floating-point identity = bit pattern (common.cuh); kept as a named step so every use of a key reads the same
+__device__ __forceinline__ uint64_t f8_canon(uint64_t v, int key_is_f64) {
+  (void)key_is_f64;
+  return v;
+}
 __device__ __forceinline__ uint32_t f8_bin(uint64_t k, int shift) { return shift >= 64 ? 0u : (uint32_t)(mix64(k) >> shift); }
 __device__ __forceinline__ uint32_t f8_bucket(uint64_t k) { return (uint32_t)((k * 0x9E3779B97F4A7C15ULL) >> 38); }
 // v[idx] for a register array without a dynamic index (which would force the array into local memory)
@@ -187,7 +191,9 @@ __global__ void __launch_bounds__(kF8Threads) fused8_join_kernel(const __grid_co
           cnt[u] = 0;
           if (r < p1) {
             const uint64_t k = f8_canon(f8_pick<PW>(pv[u], a.pkey), a.key_is_f64);
-            for (uint32_t j = heads[f8_bucket(k) & hmask]; j != kF8Nil; j = next[j]) {
+            // a NaN key joins nothing (operator== in the reference, arrow_comparator.cpp:240-243)
+            uint32_t j = (a.key_is_f64 && key_bits_is_nan(CYL_DOUBLE, k)) ? kF8Nil : heads[f8_bucket(k) & hmask];
+            for (; j != kF8Nil; j = next[j]) {
               if (f8_canon(brec[j * BW + a.bkey], a.key_is_f64) == k) {
                 if (cnt[u] == 0) first[u] = j;
                 cnt[u]++;
@@ -364,10 +370,9 @@ __global__ void __launch_bounds__(kBlkThreads) fused8_block_scatter_kernel(const
 
 template <int W>
 static int launch_block_scatter(const F8BlockArgs &a, size_t smem, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_block_scatter_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
-    attr_set = true;
   }
   fused8_block_scatter_kernel<W><<<(unsigned)a.nblocks, kBlkThreads, smem, s>>>(a);
   CYL_LAUNCH_CHECK();
@@ -398,10 +403,9 @@ static int f8_partition_blocks(const cyl_column_t *cols, int ncols, int key, int
   a.counts = counts.as<unsigned int>();
   a.bin_total = totals.as<unsigned int>();
   const size_t smem = (size_t)nbins * sizeof(unsigned int);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
-    attr_set = true;
   }
   {
     ProfScope ps("fused_join_hist", s);
@@ -652,10 +656,9 @@ static size_t rs_smem_bytes() {
 
 template <int W, bool PASS_B>
 static int launch_radix_pass(const F8RadixArgs &a, int64_t tiles_bound, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_radix_pass_kernel<W, PASS_B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<W>()));
-    attr_set = true;
   }
   int64_t grid = (int64_t)num_sms() * 2;
   if (grid > tiles_bound) grid = tiles_bound < 1 ? 1 : tiles_bound;
@@ -700,10 +703,9 @@ static int f8_bin_histogram(const F8PartArgs &a, int64_t nbins, int64_t tile_gue
     h.tile_rows = tile;
     h.nblocks = div_up(a.n, tile);
     h.bin_total = a.hist;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.first()) {
       CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
-      attr_set = true;
     }
     ProfScope ps("fused_join_hist", s);
     fused8_block_hist_kernel<<<(unsigned)h.nblocks, kBlkThreads, (size_t)nbins * sizeof(unsigned int), s>>>(h);
@@ -722,10 +724,9 @@ static int f8_bin_histogram(const F8PartArgs &a, int64_t nbins, int64_t tile_gue
     int64_t tile = div_up(tile_guess < 8192 ? 8192 : tile_guess, (int64_t)kBlkThreads * kF8PartRows) * kBlkThreads * kF8PartRows;
     h.tile_rows = tile;
     h.nblocks = div_up(a.n, tile);
-    static bool attr_set2 = false;
-    if (!attr_set2) {
+    static PerDeviceOnce attr_once2;
+    if (attr_once2.first()) {
       CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
-      attr_set2 = true;
     }
     ProfScope ps("fused_join_hist", s);
     for (int half = 0; half < 2; half++) {
@@ -846,10 +847,9 @@ static int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n,
 
 template <int BW, int PW>
 static int launch_join(const F8JoinArgs &a, int grid, size_t smem_bytes, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_join_kernel<BW, PW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-    attr_set = true;
   }
   fused8_join_kernel<BW, PW><<<grid, kF8Threads, smem_bytes, s>>>(a);
   CYL_LAUNCH_CHECK();
@@ -869,9 +869,9 @@ static int dispatch_pw(int pw, const F8JoinArgs &a, int grid, size_t smem_bytes,
 bool fused8_eligible(const cyl_column_t *lcols, int nlcols, const cyl_column_t *rcols, int nrcols) {
   if (nlcols < 1 || nrcols < 1 || nlcols > kFused8MaxCols || nrcols > kFused8MaxCols) return false;
   for (int c = 0; c < nlcols; c++)
-    if (lcols[c].byte_width != 8 || lcols[c].validity) return false;
+    if (lcols[c].byte_width != 8) return false;
   for (int c = 0; c < nrcols; c++)
-    if (rcols[c].byte_width != 8 || rcols[c].validity) return false;
+    if (rcols[c].byte_width != 8) return false;
   return true;
 }
 

@@ -37,6 +37,7 @@ struct HashJoinArgs {
   uint32_t *next;
   int64_t nb, np;
   int32_t exact;
+  int32_t nan_type;     // exact mode with a FLOAT/DOUBLE key: its type id (a NaN key matches nothing), else 0
   int32_t keep_probe;   // LEFT/RIGHT/FULL_OUTER: unmatched probe rows produce one row
   int32_t mark_build;   // FULL_OUTER: clear bsurv[j] for matched build rows
   int32_t build_right;  // orientation of the output pairs
@@ -57,6 +58,10 @@ __device__ __forceinline__ unsigned long long sanitize_tag(unsigned long long ta
 __global__ void __launch_bounds__(256) hash_build_kernel(const __grid_constant__ HashJoinArgs a) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.nb; i += (int64_t)gridDim.x * blockDim.x) {
     const unsigned long long tag = sanitize_tag(row_tag(a.bk, i, a.exact, 0), a.exact);
+    if (a.nan_type && key_bits_is_nan(a.nan_type, tag)) {  // never matched: stays a FULL_OUTER survivor, never linked
+      a.next[i] = kNil;
+      continue;
+    }
     int64_t s;
     if (tag == kEmptyTag) {
       s = a.cap_mask + 1;
@@ -87,7 +92,7 @@ __device__ __forceinline__ int64_t find_slot(const HashJoinArgs &a, unsigned lon
 __global__ void __launch_bounds__(256) hash_probe_count_kernel(const __grid_constant__ HashJoinArgs a) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.np; i += (int64_t)gridDim.x * blockDim.x) {
     const unsigned long long tag = sanitize_tag(row_tag(a.pk, i, a.exact, 0), a.exact);
-    const int64_t s = find_slot(a, tag);
+    const int64_t s = (a.nan_type && key_bits_is_nan(a.nan_type, tag)) ? -1 : find_slot(a, tag);
     uint32_t c = 0;
     if (s >= 0) {
       const uint4 raw = *reinterpret_cast<const uint4 *>(&a.table[s]);
@@ -167,6 +172,7 @@ static void fill_args(const cyl_join_plan *p, HashJoinArgs *a) {
   a->nb = p->nb;
   a->np = p->np;
   a->exact = p->exact;
+  a->nan_type = (p->exact && (p->bk.c[0].type == CYL_FLOAT || p->bk.c[0].type == CYL_DOUBLE)) ? p->bk.c[0].type : 0;
   a->keep_probe = p->join_type != CYL_JOIN_INNER;
   a->mark_build = p->join_type == CYL_JOIN_FULL_OUTER;
   a->build_right = p->build_right;
@@ -230,6 +236,11 @@ int cyl_hash_join_count(const cyl_column_t *lkeys, const cyl_column_t *rkeys, in
   p->nb = p->build_right ? nr : nl;
   p->np = p->build_right ? nl : nr;
   p->exact = is_exact_key(lk);
+  if (p->nb > (1ll << 30)) {  // slot indices are 32-bit and the table has 2 * nb slots (+ 1 reserved)
+    const long long nb = (long long)p->nb;
+    delete p;
+    return fail(CYL_CapacityError, "cyl_hash_join_count: %lld build rows (max 2^30 per GPU)", nb);
+  }
   p->cap = next_pow2(p->nb * 2 < 1024 ? 1024 : p->nb * 2);
 
 #define PLAN_TRY(expr)       \

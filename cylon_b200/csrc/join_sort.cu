@@ -88,6 +88,7 @@ struct SortJoinArgs {
   const uint32_t *lperm, *rperm;
   int64_t nl, nr;
   int32_t exact;
+  int32_t nan_type;  // exact mode with a FLOAT/DOUBLE key: its type id (a NaN key matches nothing), else 0
   int32_t keep_left, keep_right;
   uint32_t *lo, *hi;
   uint32_t *lcount;
@@ -126,8 +127,9 @@ __device__ __forceinline__ int64_t upper_bound_from(const uint64_t *a, int64_t f
 __global__ void __launch_bounds__(256) merge_count_left_kernel(const __grid_constant__ SortJoinArgs a) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.nl; i += (int64_t)gridDim.x * blockDim.x) {
     const uint64_t t = a.ltag[i];
-    const int64_t lo = lower_bound_u64(a.rtag, a.nr, t);
-    const int64_t hi = upper_bound_from(a.rtag, lo, a.nr, t);
+    const bool nan = a.nan_type && key_bits_is_nan(a.nan_type, t);
+    const int64_t lo = nan ? 0 : lower_bound_u64(a.rtag, a.nr, t);
+    const int64_t hi = nan ? 0 : upper_bound_from(a.rtag, lo, a.nr, t);
     uint32_t c = 0;
     if (a.exact) {
       c = (uint32_t)(hi - lo);
@@ -147,7 +149,9 @@ __global__ void __launch_bounds__(256) merge_mark_right_kernel(const __grid_cons
     const uint64_t t = a.rtag[q];
     const int64_t lo = lower_bound_u64(a.ltag, a.nl, t);
     bool matched = false;
-    if (a.exact) {
+    if (a.nan_type && key_bits_is_nan(a.nan_type, t)) {
+      matched = false;
+    } else if (a.exact) {
       matched = lo < a.nl && a.ltag[lo] == t;
     } else {
       const int64_t ri = a.rperm[q];
@@ -199,6 +203,7 @@ static void fill_sort_args(const cyl_join_plan *p, SortJoinArgs *a) {
   a->nl = p->nl;
   a->nr = p->nr;
   a->exact = p->exact;
+  a->nan_type = (p->exact && (p->pk.c[0].type == CYL_FLOAT || p->pk.c[0].type == CYL_DOUBLE)) ? p->pk.c[0].type : 0;
   a->keep_left = p->join_type == CYL_JOIN_LEFT || p->join_type == CYL_JOIN_FULL_OUTER;
   a->keep_right = p->join_type == CYL_JOIN_RIGHT || p->join_type == CYL_JOIN_FULL_OUTER;
   a->lo = p->lo;

@@ -62,7 +62,10 @@ struct MultiDst {
 
 __device__ __forceinline__ uint32_t row_pid(const PartArgs &a, int64_t i) {
   if (a.digit_keys) return (uint32_t)(a.digit_keys[i] >> a.digit_shift) & 0xFFu;
-  if (a.pid_in) return a.pid_in[i];
+  if (a.pid_in) {  // caller-supplied ids index shared-memory counters: an id outside [0, P) marks the row as skipped
+    const uint32_t p = a.pid_in[i];
+    return p < a.P ? p : 0xFFFFFFFFu;
+  }
   return ref_partition_of(ref_row_hash(a.keys, i), a.P, a.pow2 != 0);
 }
 
@@ -128,7 +131,7 @@ __global__ void __launch_bounds__(kPartThreads) partition_tiles_kernel(const __g
 #pragma unroll
       for (int u = 0; u < kUnroll; u++) {
         const int64_t i = start + (int64_t)(r0 + u) * 32 + lane;
-        const bool valid = i < a.n;
+        const bool valid = pid[u] != 0xFFFFFFFFu;  // past the end, or a caller-supplied id >= P
         const unsigned peers = __match_any_sync(0xffffffffu, pid[u]);
         const unsigned rank = __popc(peers & lt);
         if (MODE == PM_DEST) {
@@ -503,10 +506,9 @@ static int grid_for(int64_t ntiles, int blocks_per_sm) {
 
 template <int MODE>
 static int launch_part(const PartArgs &a, size_t smem, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (smem > 48 * 1024 && !attr_set) {
+  static PerDeviceOnce attr_once;  // the attribute belongs to the (function, device) pair
+  if (smem > 48 * 1024 && attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(partition_tiles_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    attr_set = true;
   }
   const int bps = smem > 16 * 1024 ? 2 : 8;
   partition_tiles_kernel<MODE><<<grid_for(a.ntiles, bps), kPartThreads, smem, stream>>>(a);
@@ -930,10 +932,9 @@ int cyl_partition_plan_scatter(cyl_partition_plan_t *plan, void *const *dst, con
     }
     sa.warp_bytes = (2 * kStageMaxP + 4) * (int)sizeof(uint32_t) + off;
     const size_t smem = (size_t)sa.warp_bytes * kPartWarps;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.first()) {
       CYL_CUDA(cudaFuncSetAttribute(partition_stage_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-      attr_set = true;
     }
     bool all8 = sa.bulk && plan->ncols <= 3 && a.rounds == 16;
     for (int c = 0; c < plan->ncols; c++) all8 = all8 && a.sc.width[c] == 8;

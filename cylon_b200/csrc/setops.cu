@@ -135,6 +135,7 @@ int cyl_rowset_mask(const cyl_column_t *lcols, const cyl_column_t *rcols, int32_
   a.hit = hit.as<uint8_t>();
 
   const int64_t inserted = nl + (both_inserted ? nr : 0);
+  if (inserted > (1ll << 30)) return fail(CYL_CapacityError, "cyl_rowset_mask: %lld rows to insert (max 2^30 per GPU: 32-bit slot indices)", (long long)inserted);
   const int64_t max_cap = next_pow2(inserted * 2 < 1024 ? 1024 : inserted * 2);
   int64_t cap = rowtable_initial_capacity(inserted);
   RowTableHost rt;

@@ -33,13 +33,13 @@ static cylon_table *wrap(const std::shared_ptr<cylon::Table> &t) {
   return h;
 }
 
-static cylon::compute::AggregationOpId to_op(int32_t op) {
-  switch (op) {
-    case CYL_AGG_SUM: return cylon::compute::SUM;
-    case CYL_AGG_MIN: return cylon::compute::MIN;
-    case CYL_AGG_MAX: return cylon::compute::MAX;
-    default: return cylon::compute::COUNT;
-  }
+// The C ids 0..3 and the reference's enum (SUM, MIN, MAX, COUNT, MEAN, VAR, NUNIQUE, QUANTILE, STDDEV) number alike, so an id
+// passes through unchanged and the operator's own NotImplemented check answers for the ones outside the GPU path;
+// anything that is not an enumerator at all is refused here.
+static bool to_op(int32_t op, cylon::compute::AggregationOpId *out) {
+  if (op < (int32_t)cylon::compute::SUM || op > (int32_t)cylon::compute::STDDEV) return false;
+  *out = static_cast<cylon::compute::AggregationOpId>(op);
+  return true;
 }
 
 extern "C" {
@@ -70,6 +70,11 @@ int cylon_context_init_distributed(int32_t rank, int32_t world_size, int32_t dev
 
 int cylon_context_set_stream(cylon_context_t *c, void *stream) {
   c->ctx->SetStream(stream);
+  return CYL_OK;
+}
+int cylon_context_add_config(cylon_context_t *c, const char *key, const char *value) {
+  if (!c || !key || !value) return cylb::fail(CYL_Invalid, "cylon_context_add_config: null argument");
+  c->ctx->AddConfig(key, value);
   return CYL_OK;
 }
 int cylon_context_rank(const cylon_context_t *c) { return c->ctx->GetRank(); }
@@ -202,7 +207,11 @@ int cylon_groupby(cylon_table_t *t, const int32_t *index_cols, int32_t nindex, c
   if (!t) return cylb::fail(CYL_KeyError, "Couldn't find the table");
   std::vector<int32_t> idx(index_cols, index_cols + nindex), ac(agg_cols, agg_cols + naggs);
   std::vector<cylon::compute::AggregationOpId> ops;
-  for (int i = 0; i < naggs; i++) ops.push_back(to_op(agg_ops[i]));
+  for (int i = 0; i < naggs; i++) {
+    cylon::compute::AggregationOpId op;
+    if (!to_op(agg_ops[i], &op)) return cylb::fail(CYL_Invalid, "cylon_groupby: unknown aggregation id %d", agg_ops[i]);
+    ops.push_back(op);
+  }
   std::shared_ptr<cylon::Table> o;
   Status st;
   if (distributed) {

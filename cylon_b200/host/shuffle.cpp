@@ -240,6 +240,18 @@ extern "C" int cyl_shuffle_plan(const int64_t *counts, int32_t world, int32_t ra
 
 namespace cylon {
 
+// Every rank holds the full counts matrix after the count exchange, so a capacity verdict can be reached for ALL
+// receivers and returned by all ranks together; a rank-local early return between collectives would leave the others
+// waiting in the next one.
+static Status CheckReceiveTotals(const std::vector<int64_t> &counts, int P) {
+  for (int dst = 0; dst < P; dst++) {
+    int64_t rows = 0;
+    for (int sr = 0; sr < P; sr++) rows += counts[(size_t)sr * P + dst];
+    if (rows > 0xFFFFFFFEll) return Status(Code::CapacityError, "shuffle would put more than 2^32-2 rows on rank " + std::to_string(dst));
+  }
+  return Status::OK();
+}
+
 // Fused partition + shuffle over peer memory, for tables whose columns are all fixed width (1/2/4/8/16 bytes) and carry
 // no nulls on any rank: histogram pass -> count exchange -> every rank allocates its output columns and maps the
 // others' through CUDA IPC -> ONE scatter kernel per rank writes each row straight to its final position, locally or
@@ -281,7 +293,7 @@ static Status ShufflePeerScatter(std::shared_ptr<CylonContext> &ctx, std::shared
   std::vector<int64_t> so(P), sc(P), ro(P), rc(P);
   int64_t total_rows = 0;
   CYL_RETURN_IF_FAILED(cyl_shuffle_plan(counts.data(), P, rank, so.data(), sc.data(), ro.data(), rc.data(), &total_rows));
-  if (total_rows > 0xFFFFFFFEll) return Status(Code::CapacityError, "shuffle would put more than 2^32-2 rows on one GPU");
+  RETURN_CYLON_STATUS_IF_FAILED(CheckReceiveTotals(counts, P));  // same verdict on every rank: nobody is left waiting
 
   // my output columns = what the peers write into
   std::vector<std::shared_ptr<Column>> out_cols((size_t)ncols);
@@ -355,7 +367,15 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
   CYL_RETURN_IF_FAILED(cyl_shuffle_plan(row_matrix.data(), P, rank, plan_send_off.data(), plan_send_cnt.data(), recv_row_off.data(),
                                         recv_rows.data(), &total_rows));
   recv_row_off[P] = total_rows;
-  if (total_rows > 0xFFFFFFFEll) return Status(Code::CapacityError, "shuffle would put more than 2^32-2 rows on one GPU");
+  RETURN_CYLON_STATUS_IF_FAILED(CheckReceiveTotals(row_matrix, P));  // same verdict on every rank
+  for (size_t v = 0; v < var_cols.size(); v++) {  // int32 offsets: evaluated for EVERY receiver, so all ranks return alike
+    for (int dst = 0; dst < P; dst++) {
+      int64_t bytes = 0;
+      for (int sr = 0; sr < P; sr++) bytes += at(sr, P * (1 + (int)v) + dst);
+      if (bytes > 0x7FFFFFFFll)
+        return Status(Code::CapacityError, "shuffled variable-width column exceeds 2^31-1 bytes on rank " + std::to_string(dst));
+    }
+  }
 
   std::vector<std::shared_ptr<Column>> out_cols((size_t)ncols);
   std::vector<net::Communicator::Exchange> ex;
@@ -397,7 +417,6 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
         rbytes[p] = at(p, P * (1 + vidx) + rank);
         roff[p + 1] = roff[p] + rbytes[p];
       }
-      if (roff[P] > 0x7FFFFFFFll) return Status(Code::CapacityError, "shuffled variable-width column exceeds 2^31-1 bytes on one GPU");
       RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(names[c], src->type(), 0, total_rows, roff[P], any_validity, stream, &out_cols[c]));
       // lengths travel as int32 per row; offsets are rebuilt on the receiver
       keep.emplace_back(new DevBuf());

@@ -33,11 +33,15 @@ Status CheckColumns(const Table &t, const std::vector<int> &cols, const char *wh
   return Status::OK();
 }
 
-Status GatherColumns(const Table &t, const int64_t *idx, int64_t m, bool may_be_negative, const std::string &prefix, void *stream,
-                     std::vector<std::shared_ptr<Column>> *out) {
+// keep_source_validity: true for the Filter-like uses (set operators, Unique: arrow::compute::Filter keeps nulls); false
+// for the join, whose copy_array_by_indices (util/copy_arrray.cpp:39-47) appends a null only for index -1 and otherwise
+// the value slot as it is -- a null of the input comes out as a valid row holding whatever the slot held.
+Status GatherColumns(const Table &t, const int64_t *idx, int64_t m, bool may_be_negative, bool keep_source_validity, const std::string &prefix,
+                     void *stream, std::vector<std::shared_ptr<Column>> *out) {
   for (const auto &src : t.GetColumns()) {
     const cyl_column_t &d = src->desc();
-    const bool with_validity = may_be_negative || d.validity != nullptr;
+    const uint8_t *src_validity = keep_source_validity ? d.validity : nullptr;
+    const bool with_validity = may_be_negative || src_validity != nullptr;
     std::shared_ptr<Column> col;
     if (src->is_var_width()) {
       DevBuf offs;
@@ -53,7 +57,7 @@ Status GatherColumns(const Table &t, const int64_t *idx, int64_t m, bool may_be_
           Column::Allocate(prefix + src->name(), d.type, d.byte_width, m, m * (int64_t)d.byte_width, with_validity, stream, &col));
       CYL_RETURN_IF_FAILED(cyl_gather_fixed(d.data, d.byte_width, idx, m, col->mutable_data(), nullptr, stream));
     }
-    if (with_validity) CYL_RETURN_IF_FAILED(cyl_gather_validity(d.validity, idx, m, col->mutable_validity(), stream));
+    if (with_validity) CYL_RETURN_IF_FAILED(cyl_gather_validity(src_validity, idx, m, col->mutable_validity(), stream));
     out->push_back(col);
   }
   return Status::OK();
@@ -67,7 +71,7 @@ Status FilterTable(const std::shared_ptr<Table> &t, const uint8_t *mask, std::sh
   int64_t count = 0;
   CYL_RETURN_IF_FAILED(cyl_mask_to_indices(mask, n, idx.as<int64_t>(), &count, stream));
   std::vector<std::shared_ptr<Column>> cols;
-  RETURN_CYLON_STATUS_IF_FAILED(GatherColumns(*t, idx.as<int64_t>(), count, false, "", stream, &cols));
+  RETURN_CYLON_STATUS_IF_FAILED(GatherColumns(*t, idx.as<int64_t>(), count, false, true, "", stream, &cols));
   *out = std::make_shared<Table>(std::move(cols), t->GetContext());
   return Status::OK();
 }
@@ -212,8 +216,8 @@ Status Join(std::shared_ptr<Table> &left, std::shared_ptr<Table> &right, const j
   const bool left_null = jt == CYL_JOIN_RIGHT || jt == CYL_JOIN_FULL_OUTER;
   const bool right_null = jt == CYL_JOIN_LEFT || jt == CYL_JOIN_FULL_OUTER;
   std::vector<std::shared_ptr<Column>> cols;
-  RETURN_CYLON_STATUS_IF_FAILED(detail::GatherColumns(*left, li.as<int64_t>(), m, left_null, cfg.GetLeftTableSuffix(), stream, &cols));
-  RETURN_CYLON_STATUS_IF_FAILED(detail::GatherColumns(*right, ri.as<int64_t>(), m, right_null, cfg.GetRightTableSuffix(), stream, &cols));
+  RETURN_CYLON_STATUS_IF_FAILED(detail::GatherColumns(*left, li.as<int64_t>(), m, left_null, false, cfg.GetLeftTableSuffix(), stream, &cols));
+  RETURN_CYLON_STATUS_IF_FAILED(detail::GatherColumns(*right, ri.as<int64_t>(), m, right_null, false, cfg.GetRightTableSuffix(), stream, &cols));
   out = std::make_shared<Table>(std::move(cols), ctx);
   return Status::OK();
 }

@@ -16,7 +16,8 @@ Status CheckColumns(const Table &t, const std::vector<int> &cols, const char *wh
 
 // copy_array_by_indices for every column of `t` (util/copy_arrray.cpp:142-292): out[i] = idx[i] < 0 ? null : t[idx[i]].
 // may_be_negative: idx can hold -1 (then a validity bitmap is produced); source nulls are always kept.
-Status GatherColumns(const Table &t, const int64_t *idx, int64_t m, bool may_be_negative, const std::string &prefix, void *stream,
+Status GatherColumns(const Table &t, const int64_t *idx, int64_t m, bool may_be_negative, bool keep_source_validity, const std::string &prefix,
+                     void *stream,
                      std::vector<std::shared_ptr<Column>> *out);
 // arrow::compute::Filter with a byte mask
 Status FilterTable(const std::shared_ptr<Table> &t, const uint8_t *mask, std::shared_ptr<Table> *out);

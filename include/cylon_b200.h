@@ -70,7 +70,9 @@ int cyl_hash_partition(const cyl_column_t *cols /* host array */, int32_t ncols,
 
 /* ---------------------------------------------------------------- B: split (stable scatter) ---- */
 /* dest[i] = part_offsets[pid[i]] + #{j < i : pid[j] == pid[i]}  (row order inside a partition = input order),
- * part_offsets = exclusive scan of the histogram, int64[P+1]. num_partitions <= 1024.
+ * part_offsets = exclusive scan of the histogram, int64[P+1]. num_partitions <= 1024. Every pid[i] must be below
+ * num_partitions; a row whose id is not is counted in no partition and its dest[i] is left untouched (the reference
+ * would index past its builder vector there, arrow_kernels.cpp:52).
  * Replaces the row routing of ArrowArraySplitKernel::Split (arrow/arrow_kernels.cpp:40-72). */
 int cyl_scatter_map(const uint32_t *pid, int64_t nrows, uint32_t num_partitions, int64_t *dest, int64_t *part_offsets,
                     void *stream);
@@ -157,7 +159,8 @@ void cyl_join_plan_free(cyl_join_plan_t *plan);
 /* Fused fast path of the INNER hash join: radix-partition both tables on the key hash, then build each partition's
  * hash table in SHARED memory and write the joined rows directly (no index vectors, no gather pass). Requirements
  * (cyl_hash_join_fused_supported returns 1): INNER, one key column per side of the same fixed-width type (<= 8 bytes),
- * every column fixed width (1/2/4/8 bytes) without a validity bitmap, at most 8 columns per side.
+ * every column fixed width (1/2/4/8 bytes), at most 8 columns per side. Validity bitmaps of the inputs are ignored, as the
+ * reference's join ignores them (keys compare by value slot, copy_arrray.cpp:47 drops source validity): the result has none.
  * out_cols: host array of nlcols + nrcols device pointers (left columns first, the layout build_final_table produces,
  * join/join_utils.cpp:126-181), each with room for `capacity` values. The result size is only known after probing:
  * *num_rows (host out; the call synchronises) always receives the exact count; the rows were written only if
@@ -177,7 +180,9 @@ int cyl_hash_join_fused_set_bins_log2(int32_t bits);
 
 /* ---------------------------------------------------------------- D4: gather ------------------- */
 /* dst[i] = idx[i] < 0 ? 0 : src[idx[i]]; dst_validity (may be NULL) gets bit i = (idx[i] >= 0), it has
- * ceil(m/32)*4 bytes. Source validity is not propagated, as in the reference.
+ * ceil(m/32)*4 bytes. Source validity is not propagated, as in the reference (copy_arrray.cpp:47): cylon::Join builds
+ * its result with validity = (index >= 0) only; the Filter-like callers (set operators, Unique) gather the source bitmap
+ * separately with cyl_gather_validity.
  * Replaces copy_array_by_indices (util/copy_arrray.cpp:24-50,87-110,142-292). */
 int cyl_gather_fixed(const void *src, int32_t byte_width, const int64_t *idx, int64_t m, void *dst, uint8_t *dst_validity,
                      void *stream);

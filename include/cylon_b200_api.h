@@ -25,6 +25,10 @@ int cylon_context_init(int32_t device, cylon_context_t **ctx);
 int cylon_nccl_unique_id(char id[128]); /* rank 0 creates, every rank passes the same bytes below */
 int cylon_context_init_distributed(int32_t rank, int32_t world_size, int32_t device, const char id[128], cylon_context_t **ctx);
 int cylon_context_set_stream(cylon_context_t *ctx, void *cuda_stream);
+/* CylonContext::AddConfig (ctx/cylon_context.hpp:85). Keys read by this library: "cylon.join.fused" ("0" = general hash
+ * join only), "cylon.shuffle.peer" ("0" = NCCL send/recv instead of NVLink peer stores; must be the same on every rank),
+ * "cylon.groupby.fused" / "cylon.setops.fused" ("0" = global row table only). */
+int cylon_context_add_config(cylon_context_t *ctx, const char *key, const char *value);
 int cylon_context_rank(const cylon_context_t *ctx);
 int cylon_context_world_size(const cylon_context_t *ctx);
 int cylon_context_barrier(cylon_context_t *ctx);

@@ -246,6 +246,24 @@ static inline int cmp_rows(const cyl_column_t *a, int64_t i, const cyl_column_t 
   return 0;
 }
 
+/* equal_to of the single-key hash join -- arrow_comparator.cpp:240-243: operator== on the values, so a NaN key equals
+ * nothing (cmp_value's three-way result is 0 for NaN, as the reference's subtraction trick :226-238 also yields). */
+static inline int eq_single_key(const cyl_column_t *a, int64_t i, const cyl_column_t *b, int64_t j) {
+  if (a->type == CYL_DOUBLE) {
+    double x, y;
+    memcpy(&x, (const uint8_t *)a->data + i * 8, 8);
+    memcpy(&y, (const uint8_t *)b->data + j * 8, 8);
+    return x == y;
+  }
+  if (a->type == CYL_FLOAT) {
+    float x, y;
+    memcpy(&x, (const uint8_t *)a->data + i * 4, 4);
+    memcpy(&y, (const uint8_t *)b->data + j * 4, 4);
+    return x == y;
+  }
+  return cmp_value(a, i, b, j) == 0;
+}
+
 static int64_t next_pow2(int64_t n) {
   int64_t c = 16;
   while (c < n) c <<= 1;
@@ -323,7 +341,7 @@ int orc_hash_join(const cyl_column_t *lkeys, const cyl_column_t *rkeys, int32_t 
     int found = 0;
     for (int64_t j = head[hp[i] & (nbuckets - 1)]; j >= 0; j = next[j]) {
       if (hb[j] != hp[i]) continue;
-      int eq = fast_i64 ? (bk64[j] == pk64[i]) : (cmp_rows(bk, j, pk, i, nkeys) == 0);
+      int eq = fast_i64 ? (bk64[j] == pk64[i]) : (nkeys == 1 ? eq_single_key(bk, j, pk, i) : (cmp_rows(bk, j, pk, i, nkeys) == 0));
       if (!eq) continue;
       found = 1;
       if (b_survivor) b_survivor[j] = 0;

@@ -274,3 +274,57 @@ def test_string_payload_through_join_and_shuffle_matches_reference(world):
         exp, got = orc.shuffle(lefts, [0]), pyref.dist_op(pyref.DIST_SHUFFLE, lefts, p1=[0])
         for r in range(world):
             assert_same_rows(got[r], exp[r], "shuffle rank %d" % r)
+
+
+# ---- floating-point key identity (NaN, -0.0 / +0.0, +-inf): what the reference really does, pinned --------------------
+def _special_tables(extra_key=False):
+    nan2 = np.array([0x7FF8000000000001], dtype=np.uint64).view(np.float64)[0]
+    pool = np.array([np.nan, nan2, -0.0, 0.0, np.inf, -np.inf, 1.0, 2.5, -3.0, 1e300], dtype=np.float64)
+
+    def one(n, seed, base):
+        rng = np.random.default_rng(seed)
+        cols = [orc.col(pool[rng.integers(0, len(pool), n)], name="k")]
+        if extra_key:
+            cols.append(orc.col((np.arange(n) % 2).astype(np.int64), name="z"))
+        cols.append(orc.col(np.arange(n, dtype=np.int64) + base, name="v"))
+        return cols
+    return one(400, 1, 0), one(300, 2, 10_000)
+
+
+def _bit_rows(table):
+    cols = []
+    for c in table:
+        vals = c.values()
+        if c.type == orc.DOUBLE:
+            vals = [None if v is None else b for v, b in zip(vals, c.data.view(np.uint64).tolist())]
+        cols.append(vals)
+    return sorted(zip(*cols), key=lambda r: tuple((v is None, v if v is not None else 0) for v in r))
+
+
+@pytest.mark.skipif(not pyref.dist_available(), reason="table operators of the reference not built")
+@pytest.mark.parametrize("jt", [orc.INNER, orc.LEFT, orc.RIGHT, orc.FULL_OUTER])
+@pytest.mark.parametrize("two_keys", [False, True])
+def test_float_key_identity_hash_join(jt, two_keys):
+    """Single key: operator== (a NaN joins nothing) on keys whose murmur3-of-bits hashes agree (-0.0 and +0.0 never meet).
+    Two keys: the three-way compare chain, under which NaNs with identical bits are equal."""
+    l, r = _special_tables(two_keys)
+    keys = [0, 1] if two_keys else [0]
+    ref = pyref.join_tables(l, r, keys, keys, jt, orc.HASH)
+    assert _bit_rows(orc.join(l, r, keys, keys, jt, orc.HASH)) == _bit_rows(ref)
+    if not two_keys and jt == orc.INNER:
+        assert not np.isnan(ref[0].data).any()
+        assert np.array_equal(ref[0].data.view(np.uint64), ref[2].data.view(np.uint64))
+
+
+@pytest.mark.skipif(not pyref.dist_available(), reason="table operators of the reference not built")
+@pytest.mark.parametrize("ncols", [1, 2])
+def test_float_key_identity_row_sets(ncols):
+    l, r = _special_tables(ncols == 2)
+    l, r = l[:ncols], r[:ncols]
+    for oop, rop in ((orc.UNION, pyref.DIST_UNION), (orc.INTERSECT, pyref.DIST_INTERSECT), (orc.SUBTRACT, pyref.DIST_SUBTRACT)):
+        assert _bit_rows(orc.set_op(l, r, oop)) == _bit_rows(pyref.dist_op(rop, [l], [r])[0])
+    keys = list(range(ncols))
+    assert _bit_rows(orc.unique(l, keys)) == _bit_rows(pyref.dist_op(pyref.DIST_UNIQUE, [l], p1=keys)[0])
+    full, _ = _special_tables(False)
+    ref = pyref.dist_op(pyref.DIST_GROUPBY, [full], p1=[0], p2=[1, orc.SUM, 1, orc.COUNT])[0]
+    assert _bit_rows(orc.hash_groupby(full, [0], [(1, orc.SUM), (1, orc.COUNT)])) == _bit_rows(ref)
