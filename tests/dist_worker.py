@@ -31,6 +31,8 @@ def main():
     dist.broadcast(idt, 0)
     ctx = api.CylonContext(device=local, distributed=True, rank=rank, world_size=world, nccl_id=idt.cpu().numpy().tobytes())
     assert ctx.get_rank() == rank and ctx.get_world_size() == world
+    peer = os.environ.get("CYLON_TEST_SHUFFLE_PEER", "1")
+    ctx.add_config("cylon.shuffle.peer", peer)  # "0": every shuffle takes the NCCL send/recv path, also for fixed-width tables
     checks = 0
 
     # ---- reference golden files (cpp/test/join_test.cpp, set_op_test.cpp): per-rank expected outputs at world 2 and 4
@@ -128,7 +130,7 @@ def main():
     tot = torch.tensor([checks], device="cuda")
     dist.all_reduce(tot)
     if rank == 0:
-        print("DIST_OK world=%d checks=%d" % (world, int(tot.item())))
+        print("DIST_OK world=%d peer=%s checks=%d" % (world, peer, int(tot.item())))
     ctx.finalize()
     dist.destroy_process_group()
 
