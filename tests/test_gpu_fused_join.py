@@ -60,10 +60,10 @@ def test_fused_join_key_types_and_mixed_widths(cy, key_kind):
 def test_fused_join_negative_zero_and_extremes(cy):
     l = [orc.col(np.array([0.0, -0.0, 1.5, np.finfo(np.float64).max, -1.5]))]
     r = [orc.col(np.array([-0.0, 0.0, -1.5, np.finfo(np.float64).max]))]
-    # -0.0 vs 0.0: the reference's HASH join hashes the bit pattern but compares by value, so whether they meet is an
-    # accident of its buckets ("undefined -- avoid"); its SORT join compares by value and joins them.
-    # This library always uses value equality, i.e. the SORT join's answer; each side keeps its own bits.
-    _check(cy, l, r, 0, 0, oracle_algo=orc.SORT)
+    # -0.0 vs 0.0: the reference's HASH join hashes the bit pattern and only compares keys whose hashes agree, so the two
+    # zeros never meet (run against the compiled reference: tests/test_oracle_vs_reference.py::test_float_key_identity_*).
+    # Same here: a floating-point key is identified by its bits.
+    _check(cy, l, r, 0, 0, oracle_algo=orc.HASH)
     i64 = np.iinfo(np.int64)
     l = [orc.col(np.array([-1, i64.min, i64.max, 0, -1], dtype=np.int64))]
     r = [orc.col(np.array([i64.max, -1, 7, i64.min], dtype=np.int64))]
