@@ -1,15 +1,22 @@
 #!/usr/bin/env python
-"""bench.py -- DistributedJoin throughput (input rows/s) on N B200s, with roofline and CPU baseline.
+"""bench.py -- throughput of the distributed relational hot path on N B200s, with roofline, parity and CPU baseline.
 
 Contract (see DESIGN.md "Measurement"):
   python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun, one rank per GPU)
   python bench.py --impl reference --gpus N --steps K --warmup W
+  python bench.py --config {join,sortjoin,groupby,setops,shuffle} ...     (default join = BASELINE.json configs[1])
 
-A "step" is one cylon::DistributedJoin(inner, HASH) of two (int64 key, double payload) tables with `--rows` rows per
-side per GPU (BASELINE.json configs[1]: 100M), keys uniform in [0, rows * N) (the reference's in-memory generator,
-cpp/src/examples/ra_test_inmem_datagen_example.cpp:104-120). `value` = (N_L + N_R) * N / max-over-ranks step time
-with the inputs already in HBM (CUDA events on the operator's stream); `e2e` = the same through host buffers
-(pinned H2D of both tables and D2H of the whole result inside the timed region).
+A "step" is one Distributed* operator over one batch of synthetic input (workloads.py):
+  join      cylon::DistributedJoin(inner, HASH), 100M rows per side per GPU, (int64 key, double payload), uniform keys
+  sortjoin  cylon::DistributedJoin(left|right|fullouter, SORT) on an (int64, int32) key, Zipf(1.1) left side, 50M rows per side per GPU
+  groupby   cylon::DistributedHashGroupBy(sum, count, min, max), 125M rows per GPU, 1M distinct int64 groups
+  setops    cylon::DistributedUnion|Intersect|Subtract / DistributedUnique on (int64, string, double) tables, 25M rows per GPU per table
+  shuffle   cylon::Shuffle of an (int64, double) table of --shuffle-bytes per GPU (N = 1: the hash partition + split it starts with)
+`value` = input rows of all ranks / max-over-ranks step time with the inputs already in HBM (CUDA events on the operator's
+stream); `e2e` = the same through host buffers (pinned H2D of the inputs and D2H of the whole result inside the timed
+region). After the timed steps every rank's result is checked (`parity`): the full-size row count against a closed form of
+the seeded generator, and a smaller run of the same operator, rank by rank, against the reference compiled in
+oracle/_ref (else the oracle). A mismatch makes the run exit non-zero.
 """
 import argparse
 import json
@@ -25,23 +32,18 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "DistributedJoin input rows/sec"
+import workloads  # noqa: E402
+
 UNIT = "rows/s"
+NVLINK_PEAK_GBS = 900.0  # per direction per GPU (B200_PROFILING.md: nominal; measured peer copy 770)
 
 
-def splitmix64(x):
-    with np.errstate(over="ignore"):
-        x = x + np.uint64(0x9E3779B97F4A7C15)
-        z = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
-        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
-        return z ^ (z >> np.uint64(31))
-
-
+# ---- the join benchmark's generator (kept byte for byte from round 1 so the numbers stay comparable) -------------------
 def synth_table(rows, key_range, seed, rank, out_keys=None, out_vals=None, chunk=1 << 24):
     """(int64 key uniform in [0, key_range), double payload in [DBL_MIN, 1)); deterministic in (seed, rank, row)."""
+    splitmix64 = workloads.splitmix64
     keys = out_keys if out_keys is not None else np.empty(rows, dtype=np.int64)
     vals = out_vals if out_vals is not None else np.empty(rows, dtype=np.float64)
-    # one independent counter-based stream per (seed, rank, column): random 64-bit start, then consecutive counters
     kbase = splitmix64(np.array([seed * 4096 + rank * 2 + 0], dtype=np.uint64))[0]
     vbase = splitmix64(np.array([seed * 4096 + rank * 2 + 1], dtype=np.uint64))[0]
     tiny = np.finfo(np.float64).tiny
@@ -103,128 +105,711 @@ def load_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-# algorithmic bytes per launch of each profiled kernel, per DESIGN.md "Kernels": inputs read once + outputs written once;
-# hash-table / index / scratch traffic is NOT credited. n = rows per side, m = output rows.
-def algorithmic_bytes(kernel, n, m):
-    table = {
-        "hash_join_build": n * 8,            # build keys in
-        "hash_join_probe_count": n * 8,      # probe keys in
-        "hash_join_probe_write": m * 16,     # (l, r) index pairs out
-        "hash_join_scan": n * 4 + n * 8,     # counts in, offsets out
-        "hash_join_init_slots": 0,
-        "gather_fixed": m * 8 + m * 8,       # per launch: one 8-byte column, values in + out
-        "fused_join_hist": n * 8,            # per launch (one table): keys in
-        "fused_join_offsets": 0,
-        "fused_join_scatter": n * 16 * 2,    # per launch (one table): (key, payload) columns in + packed records out
-        "fused_join_scatter_coarse": n * 16 * 2,  # per launch (one table): columns in + records ordered by coarse digit out
-        "fused_join_scatter_fine": n * 16 * 2,    # per launch (one table): records in + records ordered by bin out
-        "fused_join_probe": 2 * n * 16 + m * 32,  # both record streams in + the 4 result columns out (= SURVEY 8d local join)
-        "partition_scatter_peer": n * 16 * 2,  # per launch (one table): rows in + rows out (remote share over NVLink)
-        "partition_tile_hist": n * 8,
-        "partition_scatter": n * 16 * 2,     # whole (key, payload) table in + out
-        "partition_scan": 0,
-    }
-    return table.get(kernel, 0)
+def pinned_like(arr):
+    from cylon_b200 import capi
+    out = capi.pinned_array(len(arr), arr.dtype)
+    out[:] = arr
+    return out
 
 
-def cpu_baseline(lk, lv, rk, rv, rows_sample, threads=1):
-    """the reference's CPU join timed on this box: oracle/_ref (the reference's own JoinTables) when built, else the
-    oracle port. Returns the cpu_baseline object."""
+def pinned_columns(cols):
+    """numpy columns / (offsets, bytes) tuples -> the same in page-locked memory"""
+    return [(pinned_like(c[0]), pinned_like(c[1])) if isinstance(c, tuple) else pinned_like(c) for c in cols]
+
+
+def column_bytes(cols):
+    return int(sum((c[0].nbytes + c[1].nbytes) if isinstance(c, tuple) else c.nbytes for c in cols))
+
+
+def to_oracle(cols, names=None):
     from oracle import pyoracle as orc
-    from oracle import pyref
-    # keys of the sample keep the full workload's match rate (~1 match per probe row): fold them into [0, sample)
-    lk = lk[:rows_sample] % rows_sample
-    rk = rk[:rows_sample] % rows_sample
-    lv, rv = lv[:rows_sample], rv[:rows_sample]
-    t0 = time.perf_counter()
-    if pyref.available():
-        out = pyref.join_tables([orc.col(lk), orc.col(lv)], [orc.col(rk), orc.col(rv)], [0], [0], orc.INNER, orc.HASH)
-        m = out[0].length
-        kind = "reference"
-    else:
-        m, _cs = orc.join_i64_f64(lk, lv, rk, rv, orc.INNER, orc.HASH)
-        kind = "port"
-    dt = time.perf_counter() - t0
-    return {"value": 2 * rows_sample / dt, "unit": UNIT, "cores": threads, "kind": kind,
-            "sample": "inner hash join of %d x %d rows (keys folded into [0, %d)), %d output rows, %.2f s; "
-                      "cylon::join::JoinTables, single-threaded as one MPI rank of the reference runs"
-                      % (rows_sample, rows_sample, rows_sample, m, dt)}
+    out = []
+    for i, c in enumerate(cols):
+        name = names[i] if names else "c%d" % i
+        if isinstance(c, tuple):
+            out.append(orc.HCol(orc.STRING, np.asarray(c[1]), np.asarray(c[0]), name=name))
+        else:
+            out.append(orc.col(np.asarray(c), name=name))
+    return out
 
 
-def _ref_worker(a):
-    rows, rank = a
-    from oracle import pyoracle as orc
-    from oracle import pyref
-    lk, lv = synth_table(rows, rows, 1, rank)
-    rk, rv = synth_table(rows, rows, 2, rank)
-    t0 = time.perf_counter()
-    if pyref.available():
-        out = pyref.join_tables([orc.col(lk), orc.col(lv)], [orc.col(rk), orc.col(rv)], [0], [0], orc.INNER, orc.HASH)
-        m = out[0].length
-    else:
-        m, _ = orc.join_i64_f64(lk, lv, rk, rv, orc.INNER, orc.HASH)
-    return time.perf_counter() - t0, m
+class Env:
+    """process-wide plumbing: rank, device, torch.distributed group, library context"""
+
+    def __init__(self):
+        import torch
+
+        from cylon_b200 import api
+        self.torch = torch
+        self.api = api
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local_rank)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            self.dist = dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+        self.ctx = self.new_context()
+        self.ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+
+    def new_context(self):
+        torch, api = self.torch, self.api
+        if self.world > 1:
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if self.rank == 0:
+                idt = torch.frombuffer(bytearray(api.nccl_unique_id()), dtype=torch.uint8).cuda()
+            self.dist.broadcast(idt, 0)
+            return api.CylonContext(device=self.local_rank, distributed=True, rank=self.rank, world_size=self.world,
+                                    nccl_id=idt.cpu().numpy().tobytes())
+        return api.CylonContext(device=self.local_rank)
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def allreduce(self, values, op="sum"):
+        """list of python ints/floats -> reduced list (int64 / float64 on the device, NCCL)"""
+        torch = self.torch
+        is_float = any(isinstance(v, float) for v in values)
+        t = torch.tensor(values, dtype=torch.float64 if is_float else torch.int64, device="cuda")
+        if self.dist is not None:
+            ops = {"sum": self.dist.ReduceOp.SUM, "max": self.dist.ReduceOp.MAX, "min": self.dist.ReduceOp.MIN}
+            self.dist.all_reduce(t, op=ops[op])
+        return t.tolist()
+
+    def gather_objects(self, obj):
+        """-> list with every rank's object on rank 0 (None elsewhere)"""
+        if self.dist is None:
+            return [obj]
+        out = [None] * self.world if self.rank == 0 else None
+        self.dist.gather_object(obj, out, dst=0)
+        return out
+
+    def global_bincount(self, values, domain):
+        """int64 tensor[domain]: occurrences over ALL ranks (device; used by the closed-form row counts)"""
+        torch = self.torch
+        v = torch.from_numpy(np.ascontiguousarray(values)).cuda()
+        h = torch.bincount(v, minlength=int(domain))
+        del v
+        if self.dist is not None:
+            self.dist.all_reduce(h)
+        return h
 
 
+def split_checksum(cs):
+    return [int(cs >> 32), int(cs & 0xFFFFFFFF)]
+
+
+# ======================================================================================================== workloads
+class Workload:
+    name = ""
+    metric = ""
+    dtype = "int64"
+    default_rows = 0
+
+    def __init__(self, args, env):
+        self.args, self.env = args, env
+        self.rows = args.rows or self.default_rows
+        self.rank, self.world = env.rank, env.world
+        self.state = {}
+
+    def host_inputs(self):           # -> list of tables, each a list of pinned columns
+        raise NotImplementedError
+
+    def names(self, t):
+        return None
+
+    def run(self, tables):           # one operator call over device tables -> result table
+        raise NotImplementedError
+
+    def input_rows(self):            # input rows of this rank per step
+        raise NotImplementedError
+
+    def step_algorithmic_bytes(self, out_rows, out_bytes):
+        raise NotImplementedError
+
+    def workload_text(self):
+        raise NotImplementedError
+
+    def kernel_bytes(self, kernel, out_rows):
+        return 0
+
+    def parity(self, out_rows_full):
+        return None
+
+    def cpu_baseline(self):
+        return None
+
+    def upload(self, ctx, host_tables):
+        return [self.env.api.Table.from_numpy(ctx, t, names=self.names(i)) for i, t in enumerate(host_tables)]
+
+    def result_bytes(self, out):
+        total = 0
+        for i in range(out.column_count):
+            d, nbytes = out.column_desc(i)
+            total += nbytes + (4 * (d.length + 1) if d.type in (13, 14) else 0) + ((d.length + 7) // 8 if d.validity else 0)
+        return total
+
+
+class JoinWorkload(Workload):
+    name = "join"
+    metric = "DistributedJoin input rows/sec"
+    default_rows = 100_000_000
+
+    def host_inputs(self):
+        from cylon_b200 import capi
+        rows, key_range = self.rows, self.rows * self.world
+        lk, lv = capi.pinned_array(rows, np.int64), capi.pinned_array(rows, np.float64)
+        rk, rv = capi.pinned_array(rows, np.int64), capi.pinned_array(rows, np.float64)
+        synth_table(rows, key_range, 1, self.rank, lk, lv)
+        synth_table(rows, key_range, 2, self.rank, rk, rv)
+        return [[lk, lv], [rk, rv]]
+
+    def names(self, t):
+        return ["k", "v"]
+
+    def run(self, tables):
+        return tables[0].distributed_join(tables[1], "inner", "hash", [0], [0], "l_", "r_")
+
+    def input_rows(self):
+        return 2 * self.rows
+
+    def step_algorithmic_bytes(self, out_rows, out_bytes):
+        return 2 * self.rows * 16 + out_rows * 32  # SURVEY.md 8d: (N_L + N_R) * w + M * (w_L + w_R)
+
+    def workload_text(self):
+        return ("DistributedJoin inner hash join, %d rows per side per GPU, int64 key + double payload, uniform keys in [0, rows*N)" % self.rows)
+
+    def kernel_bytes(self, kernel, m):
+        n = self.rows
+        table = {
+            "hash_join_build": n * 8, "hash_join_probe_count": n * 8, "hash_join_probe_write": m * 16, "hash_join_scan": n * 12,
+            "gather_fixed": m * 16,
+            "fused_join_hist": n * 8,                     # per launch (one table): keys in
+            "fused_join_scatter": n * 32,                 # per launch (one table): columns in + packed records out
+            "fused_join_scatter_coarse": n * 32,          # per launch: columns in + records ordered by coarse digit out
+            "fused_join_scatter_fine": n * 32,            # per launch: records in + records ordered by bin out
+            "fused_join_probe": 2 * n * 16 + m * 32,      # both record streams in + the 4 result columns out (= SURVEY 8d local join)
+            "partition_scatter_peer": n * 32,             # per launch (one table): rows in + rows out (remote share over NVLink)
+            "partition_tile_hist": n * 8, "partition_scatter": n * 32,
+        }
+        return table.get(kernel, 0)
+
+    def parity(self, out_rows_full):
+        env, api = self.env, self.env.api
+        from oracle import pyoracle as orc
+        from oracle import pyref
+        # (1) full size: M = sum over keys of cntL[k] * cntR[k], from the generator's own keys
+        key_range = self.rows * self.world
+        lk, rk = self.state["host"][0][0], self.state["host"][1][0]
+        hl = env.global_bincount(lk, key_range)
+        hr = env.global_bincount(rk, key_range)
+        expected = int((hl * hr).sum().item())
+        del hl, hr
+        env.torch.cuda.empty_cache()
+        got = env.allreduce([int(out_rows_full)])[0]
+        # (2) the same operator on a smaller pair of tables (large enough for the two-pass staged partition), rank by rank
+        # against the reference's own DistributedJoin run on `world` ranks
+        pr = min(self.rows, self.args.parity_rows or 2_200_000)
+        sl = synth_table(pr, pr * self.world, 11, self.rank)
+        sr = synth_table(pr, pr * self.world, 12, self.rank)
+        L = api.Table.from_numpy(env.ctx, list(sl), names=["k", "v"])
+        R = api.Table.from_numpy(env.ctx, list(sr), names=["k", "v"])
+        out = L.distributed_join(R, "inner", "hash", [0], [0], "l_", "r_")
+        allr = env.gather_objects([out.row_count] + split_checksum(out.checksum()))
+        ok, checker = True, None
+        if self.rank == 0:
+            lefts = [to_oracle(synth_table(pr, pr * self.world, 11, r), ["k", "v"]) for r in range(self.world)]
+            rights = [to_oracle(synth_table(pr, pr * self.world, 12, r), ["k", "v"]) for r in range(self.world)]
+            if pyref.dist_available():
+                exp = pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0], p2=[0], join_type=orc.INNER, algorithm=orc.HASH)
+                checker = "reference (oracle/_ref cylon::DistributedJoin, %d ranks)" % self.world
+            else:
+                exp = orc.distributed_join(lefts, rights, [0], [0], orc.INNER, orc.HASH, "l_", "r_")
+                checker = "oracle (oracle/oracle.c)"
+            for r in range(self.world):
+                ok = ok and list(allr[r]) == [exp[r][0].length] + split_checksum(orc.table_checksum(exp[r]))
+        ok = bool(env.allreduce([1 if ok else 0], "min")[0])
+        return {"rows_ok": got == expected, "checksum_ok": ok, "rows": got, "expected_rows": expected,
+                "sample": "%d rows per side per rank through the same operator, per-rank row count + order-independent checksum" % pr,
+                "checker": checker}
+
+    def cpu_baseline(self):
+        from oracle import pyoracle as orc
+        from oracle import pyref
+        n = min(self.args.cpu_rows, self.rows)
+        (lk, lv), (rk, rv) = self.state["host"]
+        lk, rk = np.asarray(lk[:n]) % n, np.asarray(rk[:n]) % n  # keep ~1 match per probe row
+        lv, rv = np.asarray(lv[:n]), np.asarray(rv[:n])
+        t0 = time.perf_counter()
+        if pyref.available():
+            out = pyref.join_tables([orc.col(lk), orc.col(lv)], [orc.col(rk), orc.col(rv)], [0], [0], orc.INNER, orc.HASH)
+            m, kind = out[0].length, "reference"
+        else:
+            m, _cs = orc.join_i64_f64(lk, lv, rk, rv, orc.INNER, orc.HASH)
+            kind = "port"
+        dt = time.perf_counter() - t0
+        return {"value": 2 * n / dt, "unit": UNIT, "cores": 1, "kind": kind,
+                "sample": "inner hash join of %d x %d rows (keys folded into [0, %d)), %d output rows, %.2f s; cylon::join::JoinTables, "
+                          "single-threaded as one MPI rank of the reference runs" % (n, n, n, m, dt)}
+
+
+JT_NAMES = {"left": 1, "right": 2, "fullouter": 3, "inner": 0}
+
+
+class SortJoinWorkload(Workload):
+    name = "sortjoin"
+    metric = "DistributedJoin input rows/sec"
+    default_rows = 50_000_000
+
+    def host_inputs(self):
+        l, r = workloads.sortjoin_tables(self.rows, self.world, self.rank)
+        return [pinned_columns(l), pinned_columns(r)]
+
+    def names(self, t):
+        return ["k0", "k1", "v"]
+
+    def run(self, tables):
+        return tables[0].distributed_join(tables[1], self.args.join_type, "sort", [0, 1], [0, 1], "l_", "r_")
+
+    def input_rows(self):
+        return 2 * self.rows
+
+    def step_algorithmic_bytes(self, out_rows, out_bytes):
+        return 2 * self.rows * 20 + out_rows * 40
+
+    def workload_text(self):
+        return ("DistributedJoin %s SortJoin on an (int64, int32) key + double payload, %d rows per side per GPU, left side Zipf(1.1)-skewed "
+                "over the right side's distinct tuples" % (self.args.join_type, self.rows))
+
+    def kernel_bytes(self, kernel, m):
+        n = self.rows
+        return {"sort_join_merge": 2 * n * 20 + m * 40}.get(kernel, 0)
+
+    def _sample(self, pr, r):
+        l, rr = workloads.sortjoin_tables(pr, self.world, r, seed=13)
+        keep = np.arange(pr) % 7 != 1  # some left rows lose their partner, some right rows stay unmatched
+        return l, [c[keep] for c in rr]
+
+    def parity(self, out_rows_full):
+        env, api = self.env, self.env.api
+        from oracle import pyoracle as orc
+        from oracle import pyref
+        jt = JT_NAMES[self.args.join_type]
+        domain = self.rows * self.world
+        expected = self.rows * self.world  # every left row has exactly one partner
+        if jt in (orc.RIGHT, orc.FULL_OUTER):
+            h = env.global_bincount(self.state["host"][0][0], domain)
+            expected += domain - int((h > 0).sum().item())
+            del h
+            env.torch.cuda.empty_cache()
+        got = env.allreduce([int(out_rows_full)])[0]
+        pr = min(self.rows, self.args.parity_rows or 300_000)
+        sl, sr = self._sample(pr, self.rank)
+        L = api.Table.from_numpy(env.ctx, sl, names=self.names(0))
+        R = api.Table.from_numpy(env.ctx, sr, names=self.names(1))
+        out = L.distributed_join(R, self.args.join_type, "sort", [0, 1], [0, 1], "l_", "r_")
+        allr = env.gather_objects([out.row_count] + split_checksum(out.checksum()))
+        ok, checker = True, None
+        if self.rank == 0:
+            pairs = [self._sample(pr, r) for r in range(self.world)]
+            lefts = [to_oracle(p[0], self.names(0)) for p in pairs]
+            rights = [to_oracle(p[1], self.names(1)) for p in pairs]
+            if pyref.dist_available():
+                exp = pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0, 1], p2=[0, 1], join_type=jt, algorithm=orc.SORT)
+                checker = "reference (oracle/_ref cylon::DistributedJoin SORT, %d ranks)" % self.world
+            else:
+                exp = orc.distributed_join(lefts, rights, [0, 1], [0, 1], jt, orc.SORT, "l_", "r_")
+                checker = "oracle (oracle/oracle.c)"
+            for r in range(self.world):
+                ok = ok and list(allr[r]) == [exp[r][0].length] + split_checksum(orc.table_checksum(exp[r]))
+        ok = bool(env.allreduce([1 if ok else 0], "min")[0])
+        return {"rows_ok": got == expected, "checksum_ok": ok, "rows": got, "expected_rows": expected,
+                "sample": "%d rows per side per rank (1/7 of the right rows removed), per-rank row count + checksum" % pr, "checker": checker}
+
+    def cpu_baseline(self):
+        from oracle import pyoracle as orc
+        from oracle import pyref
+        if not pyref.dist_available():
+            return None
+        n = min(self.args.cpu_rows, self.rows)
+        l, r = workloads.sortjoin_tables(n, 1, 0, seed=13)
+        rows, dt = pyref.dist_op(pyref.DIST_JOIN, [to_oracle(l)], [to_oracle(r)], p1=[0, 1], p2=[0, 1], join_type=JT_NAMES[self.args.join_type],
+                                 algorithm=orc.SORT, rows_only=True)
+        return {"value": 2 * n / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+                "sample": "%s SortJoin of %d x %d rows, %d output rows, %.2f s, one rank" % (self.args.join_type, n, n, rows[0], dt)}
+
+
+class GroupByWorkload(Workload):
+    name = "groupby"
+    metric = "DistributedHashGroupBy input rows/sec"
+    dtype = "f64"
+    default_rows = 125_000_000
+    OPS = ["sum", "count", "min", "max"]
+
+    def host_inputs(self):
+        from cylon_b200 import capi
+        k, v = capi.pinned_array(self.rows, np.int64), capi.pinned_array(self.rows, np.float64)
+        workloads.groupby_table(self.rows, self.rank, self.args.groups, out_keys=k, out_vals=v)
+        return [[k, v]]
+
+    def names(self, t):
+        return ["k", "v"]
+
+    def run(self, tables):
+        return tables[0].groupby([0], [1] * len(self.OPS), self.OPS, distributed=True)
+
+    def input_rows(self):
+        return self.rows
+
+    def step_algorithmic_bytes(self, out_rows, out_bytes):
+        return self.rows * 16 + out_rows * 40  # SURVEY.md 8d: N * w in + G * 40 B out
+
+    def workload_text(self):
+        return ("DistributedHashGroupBy sum/count/min/max of a double over %d rows per GPU, %d distinct int64 groups" % (self.rows, self.args.groups))
+
+    def kernel_bytes(self, kernel, g):
+        n = self.rows
+        return {"groupby_fused_aggregate": n * 16 + g * 40, "groupby_insert": n * 8, "groupby_aggregate": n * 16,
+                "fused_join_hist": n * 8, "fused_join_scatter_coarse": n * 32, "fused_join_scatter_fine": n * 32, "fused_join_scatter": n * 32}.get(kernel, 0)
+
+    @staticmethod
+    def _check_rank(got, exp):
+        """one rank's result (dict of numpy columns) against the expected table: keys/count/min/max exact, sum within 1e-12"""
+        if sorted(got.keys()) != sorted(c.name for c in exp):
+            return False
+        og, oe = np.argsort(got["k"], kind="stable"), np.argsort(exp[0].data, kind="stable")
+        if len(og) != len(oe) or not np.array_equal(got["k"][og], exp[0].data[oe]):
+            return False
+        for c in exp[1:]:
+            a, b = got[c.name][og], c.data[oe]
+            if c.name.startswith("sum"):
+                if not np.allclose(a, b, rtol=1e-12, atol=0):  # BASELINE.json: floating-point aggregates within 1e-12 relative
+                    return False
+            elif not np.array_equal(a, b):
+                return False
+        return True
+
+    def parity(self, out_rows_full):
+        env, api = self.env, self.env.api
+        from oracle import pyoracle as orc
+        from oracle import pyref
+        # each group lives on exactly one rank after the shuffle: total output rows = distinct keys over all ranks
+        h = env.global_bincount(np.asarray(self.state["host"][0][0]) // 7919, self.args.groups)
+        expected = int((h > 0).sum().item())
+        del h
+        env.torch.cuda.empty_cache()
+        got = env.allreduce([int(out_rows_full)])[0]
+        pr = min(self.rows, self.args.parity_rows or 1_000_000)
+        groups = max(1, min(self.args.groups, pr // 50))
+        mine = workloads.groupby_table(pr, self.rank, groups, seed=14)
+        out = api.Table.from_numpy(env.ctx, mine, names=["k", "v"]).groupby([0], [1] * 4, self.OPS, distributed=True)
+        res = {c["name"]: c["data"] for c in out.to_host()}
+        allr = env.gather_objects(res)
+        ok, checker = True, None
+        if self.rank == 0:
+            tabs = [to_oracle(workloads.groupby_table(pr, r, groups, seed=14), ["k", "v"]) for r in range(self.world)]
+            codes = [orc.SUM, orc.COUNT, orc.MIN, orc.MAX]
+            if pyref.dist_available():
+                exp = pyref.dist_op(pyref.DIST_GROUPBY, tabs, p1=[0], p2=[x for o in codes for x in (1, o)])
+                checker = "reference (oracle/_ref cylon::DistributedHashGroupBy, %d ranks)" % self.world
+            else:
+                exp = orc.distributed_hash_groupby(tabs, [0], [1] * 4, codes)
+                checker = "oracle (oracle/oracle.c)"
+            for r in range(self.world):
+                ok = ok and self._check_rank(allr[r], exp[r])
+        ok = bool(env.allreduce([1 if ok else 0], "min")[0])
+        return {"rows_ok": got == expected, "checksum_ok": ok, "rows": got, "expected_rows": expected,
+                "sample": "%d rows per rank over %d groups: per-rank keys, counts, min, max exact, sums within 1e-12 relative, column names" % (pr, groups),
+                "checker": checker}
+
+    def cpu_baseline(self):
+        from oracle import pyoracle as orc
+        from oracle import pyref
+        if not pyref.dist_available():
+            return None
+        n = min(self.args.cpu_rows * 2, self.rows)
+        groups = max(1, min(self.args.groups, n // 125))
+        t = to_oracle(workloads.groupby_table(n, 0, groups, seed=14), ["k", "v"])
+        codes = [orc.SUM, orc.COUNT, orc.MIN, orc.MAX]
+        rows, dt = pyref.dist_op(pyref.DIST_GROUPBY, [t], p1=[0], p2=[x for o in codes for x in (1, o)], rows_only=True)
+        return {"value": n / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+                "sample": "HashGroupBy sum/count/min/max of %d rows over %d groups, %.2f s, one rank" % (n, rows[0], dt)}
+
+
+SETOP_NAMES = {"union": "DistributedUnion", "intersect": "DistributedIntersect", "subtract": "DistributedSubtract", "unique": "DistributedUnique"}
+
+
+class SetOpsWorkload(Workload):
+    name = "setops"
+    dtype = "u8"
+    default_rows = 25_000_000
+
+    @property
+    def metric(self):
+        return SETOP_NAMES[self.args.setop] + " input rows/sec"
+
+    def _tables(self, rows, rank, seed=5):
+        n = 1 if self.args.setop == "unique" else 2
+        rng = 50_000_000 if rows >= self.default_rows else max(1000, rows * self.world * 2)
+        return [workloads.setop_table(rows, rank, w, seed=seed, int_range=rng) for w in range(n)]
+
+    def host_inputs(self):
+        return [pinned_columns(t) for t in self._tables(self.rows, self.rank)]
+
+    def names(self, t):
+        return ["a", "w", "f"]
+
+    def run(self, tables):
+        if self.args.setop == "unique":
+            return tables[0].distributed_unique([0, 1])
+        return getattr(tables[0], "distributed_" + self.args.setop)(tables[1])
+
+    def input_rows(self):
+        return self.rows * (1 if self.args.setop == "unique" else 2)
+
+    def step_algorithmic_bytes(self, out_rows, out_bytes):
+        return sum(column_bytes(t) for t in self.state["host"]) + out_bytes  # every input byte once + every output byte once
+
+    def workload_text(self):
+        return ("%s on (int64, string U{4..24} from a 1M-word dictionary, double) tables, %d rows per GPU per table, second table half overlapping"
+                % (SETOP_NAMES[self.args.setop], self.rows))
+
+    def parity(self, out_rows_full):
+        env, api = self.env, self.env.api
+        from oracle import pyoracle as orc
+        op = self.args.setop
+        host = self.state["host"]
+        # closed form: rows are functions of their id, so distinct rows = distinct ids
+        domain = int(max(int(np.asarray(t[0]).max()) for t in host)) + 1
+        domain = int(env.allreduce([domain], "max")[0])
+        hl = env.global_bincount(host[0][0], domain) > 0
+        if op == "unique":
+            expected = int(hl.sum().item())
+        else:
+            hr = env.global_bincount(host[1][0], domain) > 0
+            expected = int({"union": hl | hr, "intersect": hl & hr, "subtract": hl & ~hr}[op].sum().item())
+            del hr
+        del hl
+        env.torch.cuda.empty_cache()
+        got = env.allreduce([int(out_rows_full)])[0]
+        pr = min(self.rows, self.args.parity_rows or 200_000)
+        mine = self._tables(pr, self.rank, seed=15)
+        tabs = [api.Table.from_numpy(env.ctx, t, names=self.names(0)) for t in mine]
+        out = self.run(tabs)
+        allr = env.gather_objects([out.row_count] + split_checksum(out.checksum()))
+        ok = True
+        if self.rank == 0:
+            per_rank = [self._tables(pr, r, seed=15) for r in range(self.world)]
+            lefts = [to_oracle(p[0], self.names(0)) for p in per_rank]
+            if op == "unique":
+                exp = orc.distributed_unique(lefts, [0, 1])
+            else:
+                rights = [to_oracle(p[1], self.names(0)) for p in per_rank]
+                exp = orc.distributed_set_op(lefts, rights, {"union": orc.UNION, "intersect": orc.INTERSECT, "subtract": orc.SUBTRACT}[op])
+            for r in range(self.world):
+                ok = ok and list(allr[r]) == [exp[r][0].length] + split_checksum(orc.table_checksum(exp[r]))
+        ok = bool(env.allreduce([1 if ok else 0], "min")[0])
+        return {"rows_ok": got == expected, "checksum_ok": ok, "rows": got, "expected_rows": expected,
+                "sample": "%d rows per rank per table, per-rank row count + checksum" % pr,
+                "checker": "oracle (oracle/oracle.c; the reference's cross-table string comparator is broken, SURVEY.md E3: parity unpinned)"}
+
+    def cpu_baseline(self):
+        from oracle import pyoracle as orc
+        n = min(self.args.cpu_rows, self.rows)
+        tabs = [to_oracle(t, self.names(0)) for t in self._tables(n, 0, seed=15)]
+        t0 = time.perf_counter()
+        if self.args.setop == "unique":
+            out = orc.unique(tabs[0], [0, 1])
+        else:
+            out = orc.set_op(tabs[0], tabs[1], {"union": orc.UNION, "intersect": orc.INTERSECT, "subtract": orc.SUBTRACT}[self.args.setop])
+        dt = time.perf_counter() - t0
+        return {"value": n * len(tabs) / dt, "unit": UNIT, "cores": 1, "kind": "port",
+                "sample": "%s of %d-row tables, %d output rows, %.2f s (oracle port: the reference's string comparator is unsafe to run)"
+                          % (self.args.setop, n, out[0].length, dt)}
+
+
+class ShuffleWorkload(Workload):
+    name = "shuffle"
+    metric = "Shuffle input rows/sec"
+
+    def __init__(self, args, env):
+        super().__init__(args, env)
+        self.rows = args.rows or max(1, args.shuffle_bytes // 16)
+
+    def host_inputs(self):
+        from cylon_b200 import capi
+        k, v = capi.pinned_array(self.rows, np.int64), capi.pinned_array(self.rows, np.float64)
+        synth_table(self.rows, self.rows * self.world, 7, self.rank, k, v)
+        return [[k, v]]
+
+    def names(self, t):
+        return ["k", "v"]
+
+    def run(self, tables):
+        if self.world == 1:  # Shuffle is the identity on one rank (table.cpp:910-921): time its first half, partition + split
+            parts = tables[0].hash_partition([0], self.args.partitions)
+            self.state["parts"] = parts[1:]
+            return parts[0]
+        return tables[0].shuffle([0])
+
+    def input_rows(self):
+        return self.rows
+
+    def step_algorithmic_bytes(self, out_rows, out_bytes):
+        return 2 * self.rows * 16
+
+    def workload_text(self):
+        if self.world == 1:
+            return "HashPartition of a %d-row (int64, double) table into %d partitions (the local half of Shuffle)" % (self.rows, self.args.partitions)
+        return "Shuffle of a %d-row (int64, double) table per GPU (%.1f MB per GPU)" % (self.rows, self.rows * 16 / 1e6)
+
+    def kernel_bytes(self, kernel, m):
+        return {"partition_scatter_peer": self.rows * 32, "partition_tile_hist": self.rows * 8, "partition_scatter": self.rows * 32}.get(kernel, 0)
+
+    def parity(self, out_rows_full):
+        env, api = self.env, self.env.api
+        t = api.Table.from_numpy(env.ctx, self.state["host"][0], names=["k", "v"])
+        cs_in = t.checksum()
+        if self.world == 1:
+            P = self.args.partitions
+            parts = t.hash_partition([0], P)
+            rows = sum(p.row_count for p in parts)
+            cs_out = sum(p.checksum() for p in parts) & 0xFFFFFFFFFFFFFFFF
+            placed = all(bool(np.all(np.asarray(p.to_host()[0]["data"]).astype(np.uint64).astype(np.uint32) % np.uint32(P) == np.uint32(i)))
+                         for i, p in enumerate(parts) if p.row_count)
+            return {"rows_ok": rows == self.rows, "checksum_ok": cs_out == cs_in and placed, "rows": rows, "expected_rows": self.rows,
+                    "sample": "full size: rows and order-independent checksum conserved, every row in partition (uint32)key mod P",
+                    "checker": "closed form (arrow_partition_kernels.cpp:84-87)"}
+        out = t.shuffle([0])
+        keys = np.asarray(out.to_host()[0]["data"]) if out.row_count else np.zeros(0, np.int64)
+        placed = bool(np.all(keys.astype(np.uint64).astype(np.uint32) % np.uint32(self.world) == np.uint32(self.rank))) if len(keys) else True
+        tot = env.allreduce([out.row_count] + split_checksum(out.checksum()) + split_checksum(cs_in) + [1 if placed else 0])
+        cs_o = ((tot[1] << 32) + tot[2]) & 0xFFFFFFFFFFFFFFFF  # sums of 32-bit halves, compared modulo 2^64
+        cs_i = ((tot[3] << 32) + tot[4]) & 0xFFFFFFFFFFFFFFFF
+        return {"rows_ok": tot[0] == self.rows * self.world, "checksum_ok": cs_o == cs_i and tot[5] == self.world, "rows": tot[0],
+                "expected_rows": self.rows * self.world,
+                "sample": "full size: global rows and checksum conserved, every received row satisfies (uint32)key mod world == rank",
+                "checker": "closed form (arrow_partition_kernels.cpp:84-87)"}
+
+    def cpu_baseline(self):
+        from oracle import pyref
+        if not pyref.dist_available():
+            return None
+        n = min(self.args.cpu_rows * 2, self.rows)
+        world = max(2, self.world)
+        tabs = [to_oracle(synth_table(n, n * world, 7, r), ["k", "v"]) for r in range(world)]
+        rows, dt = pyref.dist_op(pyref.DIST_SHUFFLE, tabs, p1=[0], rows_only=True)
+        return {"value": n * world / dt, "unit": UNIT, "cores": world, "kind": "reference",
+                "sample": "cylon::Shuffle of %d rows per rank on %d ranks (threads, in-memory all-to-all), %.2f s" % (n, world, dt)}
+
+
+WORKLOADS = {w.name: w for w in (JoinWorkload, SortJoinWorkload, GroupByWorkload, SetOpsWorkload, ShuffleWorkload)}
+
+
+# ======================================================================================================== reference arm
 def run_reference(args):
-    """--impl reference: the reference's CPU path on all host cores -- one single-threaded rank per core (how the
-    reference scales: MPI ranks), each joining its own already-partitioned shard pair (the shuffle is free)."""
+    """--impl reference: the reference's own Distributed* operator on all host cores -- one rank per core (how the reference
+    scales: MPI ranks; here threads of one process with an in-memory channel, oracle/ref_shim), whole operator timed."""
     if int(os.environ.get("RANK", "0")) != 0:
         return 0
-    import multiprocessing as mp
     from oracle import pyoracle as orc
     from oracle import pyref
     cores = os.cpu_count() or 1
     rows = args.ref_rows
-    if pyref.dist_available():
-        # The reference's own cylon::DistributedJoin (table.cpp:482-502: hash partition, split, Arrow all-to-all, local
-        # hash join) with one rank per host core. Ranks are threads of one process and the all-to-all goes through an
-        # in-memory channel instead of MPI (oracle/ref_shim), which can only flatter the reference.
-        lefts, rights = [], []
-        for r in range(cores):
-            lk, lv = synth_table(rows, rows * cores, 1, r)
-            rk, rv = synth_table(rows, rows * cores, 2, r)
-            lefts.append([orc.col(lk), orc.col(lv)])
-            rights.append([orc.col(rk), orc.col(rv)])
-        times, out_rows = [], 0
-        for step in range(args.warmup + args.steps):
-            per_rank, seconds = pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0], p2=[0], join_type=orc.INNER, algorithm=orc.HASH,
-                                              rows_only=True)
+    cfg = args.config
+    have_ref = pyref.dist_available()
+    if cfg == "join":
+        lefts = [to_oracle(synth_table(rows, rows * cores, 1, r), ["k", "v"]) for r in range(cores)]
+        rights = [to_oracle(synth_table(rows, rows * cores, 2, r), ["k", "v"]) for r in range(cores)]
+        call = lambda: pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0], p2=[0], join_type=orc.INNER, algorithm=orc.HASH, rows_only=True)  # noqa: E731
+        fallback = lambda: orc.distributed_join(lefts, rights, [0], [0], orc.INNER, orc.HASH)  # noqa: E731
+        per_rank_rows, metric = 2 * rows, JoinWorkload.metric
+        text = "DistributedJoin inner hash join, int64 key + double payload, uniform keys in [0, rows*ranks)"
+    elif cfg == "sortjoin":
+        jt = JT_NAMES[args.join_type]
+        pairs = [workloads.sortjoin_tables(rows, cores, r) for r in range(cores)]
+        lefts, rights = [to_oracle(p[0]) for p in pairs], [to_oracle(p[1]) for p in pairs]
+        call = lambda: pyref.dist_op(pyref.DIST_JOIN, lefts, rights, p1=[0, 1], p2=[0, 1], join_type=jt, algorithm=orc.SORT, rows_only=True)  # noqa: E731
+        fallback = lambda: orc.distributed_join(lefts, rights, [0, 1], [0, 1], jt, orc.SORT)  # noqa: E731
+        per_rank_rows, metric = 2 * rows, SortJoinWorkload.metric
+        text = "DistributedJoin %s SortJoin, (int64, int32) key, Zipf(1.1) left side" % args.join_type
+    elif cfg == "groupby":
+        tabs = [to_oracle(workloads.groupby_table(rows, r, args.groups), ["k", "v"]) for r in range(cores)]
+        codes = [orc.SUM, orc.COUNT, orc.MIN, orc.MAX]
+        call = lambda: pyref.dist_op(pyref.DIST_GROUPBY, tabs, p1=[0], p2=[x for o in codes for x in (1, o)], rows_only=True)  # noqa: E731
+        fallback = lambda: orc.distributed_hash_groupby(tabs, [0], [1] * 4, codes)  # noqa: E731
+        per_rank_rows, metric = rows, GroupByWorkload.metric
+        text = "DistributedHashGroupBy sum/count/min/max, %d groups" % args.groups
+    elif cfg == "shuffle":
+        tabs = [to_oracle(synth_table(rows, rows * cores, 7, r), ["k", "v"]) for r in range(cores)]
+        call = lambda: pyref.dist_op(pyref.DIST_SHUFFLE, tabs, p1=[0], rows_only=True)  # noqa: E731
+        fallback = lambda: orc.shuffle(tabs, [0])  # noqa: E731
+        per_rank_rows, metric = rows, ShuffleWorkload.metric
+        text = "Shuffle of an (int64, double) table"
+    else:  # setops: the reference's cross-table string comparator reads out of bounds (SURVEY.md E3) -- the oracle port is timed
+        have_ref = False
+        op = args.setop
+        per = [[workloads.setop_table(rows, r, w) for w in range(1 if op == "unique" else 2)] for r in range(cores)]
+        lefts = [to_oracle(p[0]) for p in per]
+        if op == "unique":
+            fallback = lambda: orc.distributed_unique(lefts, [0, 1])  # noqa: E731
+        else:
+            rights = [to_oracle(p[1]) for p in per]
+            code = {"union": orc.UNION, "intersect": orc.INTERSECT, "subtract": orc.SUBTRACT}[op]
+            fallback = lambda: orc.distributed_set_op(lefts, rights, code)  # noqa: E731
+        call = None
+        per_rank_rows = rows * (1 if op == "unique" else 2)
+        metric = SETOP_NAMES[op] + " input rows/sec"
+        text = "%s on (int64, string, double) tables" % SETOP_NAMES[op]
+    kind = "reference" if have_ref else "port"
+    times, out_rows = [], 0
+    for step in range(args.warmup + args.steps):
+        if have_ref:
+            per_rank, seconds = call()
             out_rows = sum(per_rank)
-            if step >= args.warmup:
-                times.append(seconds)
-        ms = 1e3 * float(np.mean(times))
-        value = 2.0 * rows * cores / (ms / 1e3)
-        sample = ("cylon::DistributedJoin of the reference, %d ranks (threads, in-memory all-to-all) x (%d x %d rows), %d output rows "
-                  "per step, whole operator timed" % (cores, rows, rows, out_rows))
-        line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "int64", "data": "synthetic",
-                "config": {"workload": "DistributedJoin inner hash join, int64 key + double payload, uniform keys in [0, rows*ranks); CPU "
-                                       "sample of %d rows per side per rank, %d ranks (one per host core)" % (rows, cores)},
-                "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
-                "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
-        return 0
-    times = []
-    with mp.get_context("fork").Pool(cores) as pool:
-        for step in range(args.warmup + args.steps):
-            res = pool.map(_ref_worker, [(rows, r) for r in range(cores)])
-            if step >= args.warmup:
-                times.append(max(r[0] for r in res))
+        else:
+            t0 = time.perf_counter()
+            res = fallback()
+            seconds = time.perf_counter() - t0
+            out_rows = sum(t[0].length for t in res)
+        if step >= args.warmup:
+            times.append(seconds)
     ms = 1e3 * float(np.mean(times))
-    value = 2.0 * rows * cores / (ms / 1e3)
-    kind = "reference" if pyref.available() else "port"
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+    used = cores if have_ref else 1
+    value = float(per_rank_rows) * cores / (ms / 1e3)
+    sample = ("%s of the %s, %d ranks (%s) x %d input rows per rank, %d output rows per step, whole operator timed"
+              % (text, "reference (oracle/_ref)" if have_ref else "oracle port", cores,
+                 "threads, in-memory all-to-all" if have_ref else "simulated in one thread", per_rank_rows, out_rows))
+    line = {"impl": "reference", "metric": metric, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int64", "data": "synthetic",
-            "config": {"workload": "inner hash join, int64 key + double payload, uniform keys; CPU sample of %d rows per side per rank, "
-                                   "%d single-threaded ranks (one per host core), shards pre-partitioned" % (rows, cores)},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                             "sample": "%d ranks x (%d x %d rows) per step, timed join only (max over ranks)" % (cores, rows, rows)},
+            "dtype": WORKLOADS[cfg].dtype, "data": "synthetic",
+            "config": {"workload": "%s; CPU sample of %d rows per table per rank, %d ranks (one per host core)" % (text, rows, cores)},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": used, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
     return 0
+
+
+# ======================================================================================================== GPU arm
+def download_result(out, host_cols):
+    """device -> host copy of every buffer of the result table into preallocated pinned buffers (data, offsets)"""
+    import ctypes as C
+
+    from cylon_b200 import capi
+    total = 0
+    for c in range(out.column_count):
+        d, nbytes = out.column_desc(c)
+        data, offs = host_cols[c]
+        assert nbytes <= data.nbytes, "result column %d: %d bytes, host buffer has %d" % (c, nbytes, data.nbytes)
+        capi.check(capi.lib().cylon_table_column_to_host(out._h, C.c_int32(c), C.c_void_p(data.ctypes.data),
+                                                         C.c_void_p(offs.ctypes.data) if offs is not None else None, None))
+        total += nbytes + (4 * (d.length + 1) if offs is not None else 0)
+    return total
 
 
 def main():
@@ -233,68 +818,53 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--rows", type=int, default=100_000_000, help="rows per side per GPU (BASELINE configs[1]: 100M)")
+    ap.add_argument("--config", default="join", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="rows per table per GPU (default: the BASELINE.json size of the config)")
+    ap.add_argument("--join-type", default="left", choices=["left", "right", "fullouter", "inner"], help="sortjoin")
+    ap.add_argument("--setop", default="union", choices=["union", "intersect", "subtract", "unique"], help="setops")
+    ap.add_argument("--groups", type=int, default=1_000_000, help="groupby: distinct keys")
+    ap.add_argument("--shuffle-bytes", type=int, default=1 << 30, help="shuffle: table bytes per GPU")
+    ap.add_argument("--partitions", type=int, default=8, help="shuffle at N=1: number of partitions")
     ap.add_argument("--cpu-rows", type=int, default=4_000_000, help="rows per side of the CPU baseline sample")
-    ap.add_argument("--ref-rows", type=int, default=2_000_000, help="--impl reference: rows per side per rank")
+    ap.add_argument("--ref-rows", type=int, default=2_000_000, help="--impl reference: rows per table per rank")
+    ap.add_argument("--parity-rows", type=int, default=0, help="rows per rank of the parity sample (0 = per-config default)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-lanes", type=int, default=3, help="N=1 only: steps kept in flight by the e2e arm (one host thread + stream each)")
+    ap.add_argument("--e2e-lanes", type=int, default=3, help="steps kept in flight by the e2e arm (one host thread + stream each)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
 
-    import ctypes as C
+    from cylon_b200 import capi
 
-    import torch
+    env = Env()
+    torch, rank, world = env.torch, env.rank, env.world
+    wl = WORKLOADS[args.config](args, env)
+    host = wl.host_inputs()
+    wl.state["host"] = host
 
-    from cylon_b200 import api, capi
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt = torch.frombuffer(bytearray(api.nccl_unique_id()), dtype=torch.uint8).cuda()
-        dist.broadcast(idt, 0)
-        ctx = api.CylonContext(device=local_rank, distributed=True, rank=rank, world_size=world, nccl_id=idt.cpu().numpy().tobytes())
-    else:
-        ctx = api.CylonContext(device=local_rank)
-    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-
-    rows = args.rows
-    key_range = rows * world
-    # pinned host copies of both tables (the e2e arm copies from these every step)
-    lk, lv = capi.pinned_array(rows, np.int64), capi.pinned_array(rows, np.float64)
-    rk, rv = capi.pinned_array(rows, np.int64), capi.pinned_array(rows, np.float64)
-    synth_table(rows, key_range, 1, rank, lk, lv)
-    synth_table(rows, key_range, 2, rank, rk, rv)
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
+    def free_parts():
+        for p in wl.state.pop("parts", None) or []:
+            p.free()
 
     # ---------------------------------------------------------------- device-resident arm (`value`)
-    left = api.Table.from_numpy(ctx, [lk, lv], names=["k", "v"])
-    right = api.Table.from_numpy(ctx, [rk, rv], names=["k", "v"])
-    state = {"rows": 0}
+    tables = wl.upload(env.ctx, host)
+    info = {"rows": 0, "bytes": 0}
 
     def step():
-        out = left.distributed_join(right, "inner", "hash", [0], [0], "l_", "r_")
-        state["rows"] = out.row_count
+        out = wl.run(tables)
+        info["rows"] = out.row_count
+        if not info["bytes"]:
+            info["bytes"] = wl.result_bytes(out)
         out.free()
+        free_parts()
 
-    sampler = ClockSampler(local_rank)  # samples through warm-up, the timed steps and the e2e steps (all under load)
+    sampler = ClockSampler(env.local_rank)  # samples through warm-up, the timed steps and the e2e steps (all under load)
     sampler.start()
     for _ in range(args.warmup):
         step()
-    barrier()
+    env.barrier()
     launches0 = capi.launch_count()
     capi.profile_enable(True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -302,101 +872,109 @@ def main():
     for _ in range(args.steps):
         step()
     ev1.record()
-    barrier()
+    env.barrier()
     launches = capi.launch_count() - launches0
     capi.profile_enable(False)
     prof = capi.profile_report()
-    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_per_step = float(t.item()) / args.steps
-    value = 2.0 * rows * world / (ms_per_step / 1e3)
-    out_rows = state["rows"]
+    ms_per_step = env.allreduce([float(ev0.elapsed_time(ev1))], "max")[0] / args.steps
+    value = float(wl.input_rows()) * world / (ms_per_step / 1e3)
+    out_rows, out_bytes = info["rows"], info["bytes"]
 
     # ---------------------------------------------------------------- end-to-end arm (`e2e`): host buffers in and out
     e2e = None
     if not args.no_e2e:
-        cap = int(out_rows * 1.05) + 1024
-        host_out = [capi.pinned_array(cap, np.int64), capi.pinned_array(cap, np.float64), capi.pinned_array(cap, np.int64),
-                    capi.pinned_array(cap, np.float64)]
+        probe = wl.run(tables)  # result shape -> pinned buffers with slack (row counts differ a little between ranks' steps)
+        shapes = []
+        for c in range(probe.column_count):
+            d, nbytes = probe.column_desc(c)
+            shapes.append((int(nbytes * 1.05) + 4096, int(d.length * 1.05) + 1024 if d.type in (13, 14) else 0))
+        probe.free()
+        free_parts()
 
-        def e2e_step(cx=ctx, outs=host_out):
-            l = api.Table.from_numpy(cx, [lk, lv], names=["k", "v"])
-            r = api.Table.from_numpy(cx, [rk, rv], names=["k", "v"])
-            out = l.distributed_join(r, "inner", "hash", [0], [0], "l_", "r_")
+        def new_out_bufs():
+            return [(capi.pinned_array(nb, np.uint8), capi.pinned_array(no + 1, np.int32) if no else None) for nb, no in shapes]
+
+        d2h_bytes = [0]
+
+        def e2e_step(cx, outs):
+            tabs = wl.upload(cx, host)
+            out = wl.run(tabs)
             mm = out.row_count
-            assert mm <= cap
-            for c in range(4):
-                capi.check(capi.lib().cylon_table_column_to_host(out._h, C.c_int32(c), C.c_void_p(outs[c].ctypes.data), None, None))
+            d2h_bytes[0] = download_result(out, outs)
             out.free()
-            l.free()
-            r.free()
+            free_parts()
+            for t in tabs:
+                t.free()
             return mm
 
-        # One GPU: two steps in flight. Two host threads, each with its own CylonContext on its own stream and its own
-        # pinned result buffers, take alternate steps, so one step's result download (PCIe up) overlaps the next step's
-        # input upload (PCIe down). Every step still uploads all of its inputs and downloads its whole result inside
-        # the timed region. With torchrun (N > 1) steps stay strictly one after another on the single NCCL communicator.
-        lanes = [(ctx, host_out)]
+        # Several steps in flight: host threads, each with its own CylonContext (at N > 1 its own NCCL communicator) on its
+        # own stream and its own pinned result buffers, take alternate steps, so one step's result download (PCIe up)
+        # overlaps the next step's input upload (PCIe down) and the operator of a third. Every step still uploads all of
+        # its inputs and downloads its whole result inside the timed region. Lane i of every rank runs the same sequence
+        # of steps on communicator i, so the collectives of one lane never wait for another lane's.
+        nlanes = max(1, min(args.e2e_lanes, args.steps))
+        if args.config == "shuffle" and world == 1:
+            nlanes = 1  # wl.state["parts"] is per process
+        lanes = [(env.ctx, new_out_bufs())]
         lane_streams = []
-        if world == 1 and args.steps >= 2:
-            import threading
-            for _ in range(1, max(1, min(args.e2e_lanes, args.steps))):
-                cx = api.CylonContext(device=local_rank)
-                lane_streams.append(torch.cuda.Stream())
-                cx.set_stream(lane_streams[-1].cuda_stream)
-                lanes.append((cx, [capi.pinned_array(cap, a.dtype) for a in host_out]))
+        for _ in range(1, nlanes):
+            cx = env.new_context()
+            lane_streams.append(torch.cuda.Stream())
+            cx.set_stream(lane_streams[-1].cuda_stream)
+            lanes.append((cx, new_out_bufs()))
         for cx, outs in lanes:
             e2e_step(cx, outs)
-        barrier()
+        env.barrier()
         t0 = time.perf_counter()
+        errors = []
+
+        def lane_main(li):
+            try:
+                torch.cuda.set_device(env.local_rank)  # the CUDA current device is per host thread
+                for _s in range(li, args.steps, len(lanes)):
+                    e2e_step(*lanes[li])
+            except BaseException as exc:  # a failed lane must fail the run, not vanish with its thread
+                errors.append(exc)
+
         if len(lanes) == 1:
-            ev0.record()
-            for _ in range(args.steps):
-                mm = e2e_step()
-            ev1.record()
-            barrier()
-            wall_ms = max(ev0.elapsed_time(ev1), 1e3 * (time.perf_counter() - t0))
+            lane_main(0)
         else:
-            got = [0] * len(lanes)
-
-            errors = []
-
-            def lane_main(li):
-                try:
-                    torch.cuda.set_device(local_rank)  # the CUDA current device is per host thread
-                    for sidx in range(li, args.steps, len(lanes)):
-                        got[li] = e2e_step(*lanes[li])
-                except BaseException as exc:  # a failed lane must fail the run, not vanish with its thread
-                    errors.append(exc)
-
             threads = [threading.Thread(target=lane_main, args=(li,)) for li in range(len(lanes))]
             for th in threads:
                 th.start()
             for th in threads:
                 th.join()
-            if errors:
-                raise errors[0]
-            torch.cuda.synchronize()
-            wall_ms = 1e3 * (time.perf_counter() - t0)  # host clock around all K steps: spans both streams
-            mm = got[0]
-            assert all(g == mm for g in got)
-            for cx, _ in lanes[1:]:
-                cx.finalize()
-        te = torch.tensor([wall_ms], dtype=torch.float64, device="cuda")
-        if dist is not None:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e_ms = float(te.item()) / args.steps
-        e2e = {"value": 2.0 * rows * world / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(2 * rows * 16),
-               "d2h_bytes_per_step": int(mm * 32), "ms_per_step": e2e_ms, "steps_in_flight": len(lanes),
-               "timed_with": "host clock around all steps, device synchronised on both sides"}
-
+        if errors:
+            raise errors[0]
+        torch.cuda.synchronize()
+        wall_ms = 1e3 * (time.perf_counter() - t0)  # host clock around all K steps: spans every lane's stream
+        env.barrier()
+        for cx, _ in lanes[1:]:
+            cx.finalize()
+        e2e_ms = env.allreduce([float(wall_ms)], "max")[0] / args.steps
+        h2d = sum(column_bytes(t) for t in host)
+        e2e = {"value": float(wl.input_rows()) * world / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h_bytes[0]), "ms_per_step": e2e_ms, "steps_in_flight": len(lanes),
+               "pcie_GBps_per_rank": round((h2d + d2h_bytes[0]) / 1e9 / (e2e_ms / 1e3), 2),
+               "timed_with": "host clock around all steps, device synchronised on both sides, max over ranks"}
     sampler.stop_flag.set()
-    if rank != 0:
-        ctx.finalize()
-        return 0
 
-    # ---------------------------------------------------------------- roofline of the dominant kernel
+    # ---------------------------------------------------------------- parity (after every timed region)
+    parity = None
+    if not args.no_parity:
+        for t in tables:
+            t.free()
+        tables = []
+        parity = wl.parity(out_rows)
+    parity_bad = parity is not None and not (parity["rows_ok"] and parity["checksum_ok"])
+
+    if rank != 0:
+        env.ctx.finalize()
+        if world > 1:
+            env.dist.destroy_process_group()
+        return 3 if parity_bad else 0
+
+    # ---------------------------------------------------------------- roofline of the dominant kernel (rank 0's launches)
     peak, peak_src = load_peaks()
     m = out_rows
     dominant, dom_ms, dom_n = None, 0.0, 1
@@ -405,49 +983,59 @@ def main():
         if ms > dom_ms:
             dominant, dom_ms, dom_n = name, ms, n_l
         per_launch_ms = ms / max(1, n_l)
-        ab = algorithmic_bytes(name, rows, m)
+        ab = wl.kernel_bytes(name, m)
         kernels[name] = {"launches_per_step": n_l / args.steps, "ms_per_launch": round(per_launch_ms, 4),
                          "share_of_step": round(ms / args.steps / ms_per_step, 4),
-                         "algorithmic_GBps": round(ab / 1e9 / (per_launch_ms / 1e3), 1) if per_launch_ms > 0 else None}
+                         "algorithmic_GBps": round(ab / 1e9 / (per_launch_ms / 1e3), 1) if per_launch_ms > 0 and ab else None}
     roofline = None
     if dominant is not None:
         per_launch_ms = dom_ms / max(1, dom_n)
-        ab = algorithmic_bytes(dominant, rows, m)
-        achieved = ab / 1e9 / (per_launch_ms / 1e3)
-        # dram__bytes_read+write per launch from the committed `ncu --set full` capture (only valid for the size it was taken at)
-        traffic = None
-        scope_to_kernel = {"fused_join_scatter": "void fused8_scatter_kernel<2>", "fused_join_probe": "void fused8_join_kernel<2, 2>",
-                           "fused_join_scatter_coarse": "void fused8_radix_pass_kernel<2, 0>", "fused_join_scatter_fine": "void fused8_radix_pass_kernel<2, 1>",
-                           "fused_join_hist": "fused8_block_hist_kernel"}
-        try:
-            if rows == 100_000_000:
-                with open(os.path.join(ROOT, "profiles", "r01_traffic_100M.json")) as f:
-                    traffic = json.load(f).get(scope_to_kernel.get(dominant, ""))
-        except Exception:
+        ab = wl.kernel_bytes(dominant, m)
+        if dominant == "partition_scatter_peer" and world > 1:
+            # NVLink-bound: bytes that leave this GPU per launch = (P-1)/P of the table, against 900 GB/s per direction
+            out_b = wl.rows * 16 * (world - 1) / world
+            ach = out_b / 1e9 / (per_launch_ms / 1e3)
+            roofline = {"kernel": dominant, "bound": "nvlink", "achieved": ach, "peak": NVLINK_PEAK_GBS, "unit": "GB/s", "frac": ach / NVLINK_PEAK_GBS,
+                        "traffic": None, "peak_source": "nominal NVLink 5 per direction per GPU (measured peer copy: 770 GB/s, B200_PROFILING.md)",
+                        "algorithmic_bytes_per_launch": out_b, "ms_per_launch": per_launch_ms}
+        else:
+            achieved = ab / 1e9 / (per_launch_ms / 1e3)
             traffic = None
-        roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab, "ms_per_launch": per_launch_ms}
-    # whole local join against its algorithmic bytes ((N_L+N_R)*w + M*(w_L+w_R))
-    step_bytes = 2 * rows * 16 + m * 32
+            try:  # dram__bytes_read+write per launch from the committed `ncu --set full` capture (valid for the size it was taken at)
+                with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+                    traffic = json.load(f).get("%s@%d" % (dominant, wl.rows))
+            except Exception:
+                traffic = None
+            roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                        "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": ab, "ms_per_launch": per_launch_ms}
+    step_bytes = wl.step_algorithmic_bytes(m, out_bytes)
     step_roofline = {"algorithmic_bytes": step_bytes, "achieved_GBps": step_bytes / 1e9 / (ms_per_step / 1e3),
-                     "frac_of_peak": step_bytes / 1e9 / (ms_per_step / 1e3) / peak}
+                     "frac_of_peak": step_bytes / 1e9 / (ms_per_step / 1e3) / peak,
+                     "note": "whole operator on rank 0's shard against the HBM peak (SURVEY.md 8d bytes); at N > 1 the step also holds the NVLink exchange"}
 
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int64",
+    line = {"metric": wl.metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype,
             "data": "synthetic",
-            "config": {"workload": "DistributedJoin inner hash join, %d rows per side per GPU, int64 key + double payload, uniform keys in [0, rows*N)"
-                                   % rows, "rows_per_side_per_gpu": rows, "output_rows_rank0": m, "parallelism": "hash-partitioned, %d GPU(s)" % world,
-                       "l2": "inputs (%.1f GB per step) far exceed the 126 MB L2; no flush needed" % (2 * rows * 16 / 1e9)},
+            "config": {"workload": wl.workload_text(), "rows_per_table_per_gpu": wl.rows, "output_rows_rank0": m,
+                       "parallelism": "hash-partitioned, %d GPU(s)" % world,
+                       "l2": "inputs (%.2f GB per step per GPU) exceed the 126 MB L2; no flush needed" % (sum(column_bytes(t) for t in host) / 1e9)},
             "gpu_launches": launches, "clocks": sampler.summary(), "roofline": roofline, "step_roofline": step_roofline,
             "kernels": kernels}
     if e2e is not None:
         line["e2e"] = e2e
+    if parity is not None:
+        line["parity"] = parity
     if not args.no_cpu and world == 1:
-        line["cpu_baseline"] = cpu_baseline(np.asarray(lk), np.asarray(lv), np.asarray(rk), np.asarray(rv), min(args.cpu_rows, rows))
+        cb = wl.cpu_baseline()
+        if cb is not None:
+            line["cpu_baseline"] = cb
     print(json.dumps(line), flush=True)
-    ctx.finalize()
+    env.ctx.finalize()
     if world > 1:
-        dist.destroy_process_group()
+        env.dist.destroy_process_group()
+    if parity_bad:
+        print("PARITY MISMATCH: %r" % (parity,), file=sys.stderr)
+        return 3
     return 0
 
 
