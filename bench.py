@@ -482,8 +482,9 @@ class GroupByWorkload(Workload):
         """one rank's result (dict of numpy columns) against the expected table: keys/count/min/max exact, sum within 1e-12"""
         if sorted(got.keys()) != sorted(c.name for c in exp):
             return False
-        og, oe = np.argsort(got["k"], kind="stable"), np.argsort(exp[0].data, kind="stable")
-        if len(og) != len(oe) or not np.array_equal(got["k"][og], exp[0].data[oe]):
+        kname = exp[0].name
+        og, oe = np.argsort(got[kname], kind="stable"), np.argsort(exp[0].data, kind="stable")
+        if len(og) != len(oe) or not np.array_equal(got[kname][og], exp[0].data[oe]):
             return False
         for c in exp[1:]:
             a, b = got[c.name][og], c.data[oe]
@@ -507,12 +508,13 @@ class GroupByWorkload(Workload):
         pr = min(self.rows, self.args.parity_rows or 1_000_000)
         groups = max(1, min(self.args.groups, pr // 50))
         mine = workloads.groupby_table(pr, self.rank, groups, seed=14)
-        out = api.Table.from_numpy(env.ctx, mine, names=["k", "v"]).groupby([0], [1] * 4, self.OPS, distributed=True)
+        # the checker library names its input columns c0, c1: same names here, so the output names compare too
+        out = api.Table.from_numpy(env.ctx, mine, names=["c0", "c1"]).groupby([0], [1] * 4, self.OPS, distributed=True)
         res = {c["name"]: c["data"] for c in out.to_host()}
         allr = env.gather_objects(res)
         ok, checker = True, None
         if self.rank == 0:
-            tabs = [to_oracle(workloads.groupby_table(pr, r, groups, seed=14), ["k", "v"]) for r in range(self.world)]
+            tabs = [to_oracle(workloads.groupby_table(pr, r, groups, seed=14), ["c0", "c1"]) for r in range(self.world)]
             codes = [orc.SUM, orc.COUNT, orc.MIN, orc.MAX]
             if pyref.dist_available():
                 exp = pyref.dist_op(pyref.DIST_GROUPBY, tabs, p1=[0], p2=[x for o in codes for x in (1, o)])
