@@ -840,6 +840,9 @@ def main():
 
     from cylon_b200 import capi
 
+    for kv in filter(None, os.environ.get("CYLON_TUNE", "").split(",")):  # e.g. CYLON_TUNE=1=0,2=1 (cyl_tune_set: A/B timing of equivalent kernels)
+        k, v = kv.split("=")
+        capi.check(capi.lib().cyl_tune_set(int(k), int(v)))
     env = Env()
     torch, rank, world = env.torch, env.rank, env.world
     wl = WORKLOADS[args.config](args, env)

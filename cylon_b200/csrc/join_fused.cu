@@ -327,6 +327,11 @@ int cyl_hash_join_fused_supported(const cyl_column_t *lcols, int32_t nlcols, int
   return plan_smem(lcols, nlcols, &pl) && plan_smem(rcols, nrcols, &pl) ? 1 : 0;
 }
 
+int cyl_tune_set(int32_t key, int32_t value) {
+  fused8_tune(key, value);
+  return CYL_OK;
+}
+
 int cyl_hash_join_fused_set_bins_log2(int32_t bits) {
   if (bits < 0 || bits > 18) return fail(CYL_Invalid, "cyl_hash_join_fused_set_bins_log2: bits must be in [0, 18], got %d", bits);
   fused8_force_bins_log2(bits);

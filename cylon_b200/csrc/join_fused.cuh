@@ -10,4 +10,6 @@ int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const 
                 void *const *bout, void *const *pout, int64_t capacity, int64_t *num_rows, cudaStream_t s);
 // Test hook: force 2^bits bins in fused8_join (0 = choose from the build size). More bins than needed is always valid.
 void fused8_force_bins_log2(int bits);
+// Measurement knobs (cyl_tune_set): key 1 = tile ranking of the radix passes, key 2 = chain linking of the join.
+void fused8_tune(int key, int value);
 }  // namespace cylb

@@ -117,31 +117,16 @@ struct F8JoinArgs {
   unsigned int *work_counter;
 };
 
-// One CTA joins one bin: the bin's build records are copied into shared memory as one flat coalesced block and linked
-// into a chained table (16-bit heads, 16-bit links), then the bin's probe records stream through in tiles of 2048.
-//
-// The chains are linked WITHOUT atomics. A returning shared-memory atomic costs the whole SM ~2 cycles per lane (the
-// atomicExch version spent ~0.7 ms of a 100M-row probe on it); plain loads and stores run at 32 lanes per cycle. So rows
-// are inserted in rounds: every pending row reads the head of its bucket, all of them store their own index there (one
-// store wins), and the row whose index stayed becomes the new head with the old head as its link; the others try again.
-// A bucket with c rows takes c rounds -- 4-6 for random keys at <= 0.5 rows per bucket -- and rows still pending after
-// kF8BuildRounds (heavy duplicates of one key) fall back to atomicExch.
-//
-// The probe remembers the first two matching build rows while counting, so the usual row (0-2 matches) never walks its
-// chain a second time when it writes.
-constexpr int kF8BuildRounds = 10;
-constexpr int kF8MaxRowsPerThread = 16384 / kF8Threads;  // cap_rows <= 16384 (16-bit links)
-
 template <int BW, int PW>
-__global__ void __launch_bounds__(kF8Threads, 2) fused8_join_kernel(const __grid_constant__ F8JoinArgs a) {
+__global__ void __launch_bounds__(kF8Threads) fused8_join_kernel(const __grid_constant__ F8JoinArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ unsigned int s_bin;
   __shared__ unsigned int s_warp_tot[kF8ProbeRows][kF8Threads / 32];
   __shared__ unsigned long long s_base;
   __shared__ unsigned int s_total;
   uint64_t *brec = reinterpret_cast<uint64_t *>(smem);                                  // [cap_rows][BW]
-  uint16_t *heads = reinterpret_cast<uint16_t *>(smem + (size_t)a.cap_rows * BW * 8);   // [nheads]
-  uint16_t *next = heads + a.nheads;                                                    // [cap_rows]
+  uint32_t *heads = reinterpret_cast<uint32_t *>(smem + (size_t)a.cap_rows * BW * 8);   // [nheads]
+  uint16_t *next = reinterpret_cast<uint16_t *>(heads + a.nheads);                      // [cap_rows]
   const uint32_t hmask = (uint32_t)a.nheads - 1;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -158,92 +143,40 @@ __global__ void __launch_bounds__(kF8Threads, 2) fused8_join_kernel(const __grid
     for (int64_t c0 = b0; c0 < b1; c0 += a.cap_rows) {  // more than one chunk only under key skew
       const int nb = (int)((b1 - c0) < a.cap_rows ? (b1 - c0) : a.cap_rows);
       __syncthreads();
-      {  // heads = nil: 128-bit stores
-        uint4 *h4 = reinterpret_cast<uint4 *>(heads);
-        for (int h = tid; h < a.nheads / 8; h += kF8Threads) h4[h] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-      }
+      for (int h = tid; h < a.nheads; h += kF8Threads) heads[h] = kF8Nil;
       {  // the bin's records are contiguous: one flat coalesced copy into shared memory
         const uint64_t *src = a.brec + c0 * BW;
         const int nwords = nb * BW;
         if constexpr (BW % 2 == 0) {
           const ulonglong2 *s2 = reinterpret_cast<const ulonglong2 *>(src);
           ulonglong2 *d2 = reinterpret_cast<ulonglong2 *>(brec);
-          for (int i = tid; i < nwords / 2; i += kF8Threads) d2[i] = __ldcs(s2 + i);
+          for (int i = tid; i < nwords / 2; i += kF8Threads) d2[i] = s2[i];
         } else {
-          for (int i = tid; i < nwords; i += kF8Threads) brec[i] = ld_stream_u64(src + i);
+          for (int i = tid; i < nwords; i += kF8Threads) brec[i] = src[i];
         }
       }
       __syncthreads();
-      {  // link the chunk's rows into the chained table, in rounds of plain stores
-        uint32_t pending = 0;  // bit k: row tid + k * kF8Threads still has to be linked
-#pragma unroll
-        for (int k = 0; k < kF8MaxRowsPerThread; k++)
-          if (tid + k * kF8Threads < nb) pending |= 1u << k;
-        for (int round = 0; round < kF8BuildRounds; round++) {
-          uint16_t old[kF8MaxRowsPerThread];
-#pragma unroll
-          for (int k = 0; k < kF8MaxRowsPerThread; k++) {
-            if (pending & (1u << k)) {
-              const int i = tid + k * kF8Threads;
-              old[k] = heads[f8_bucket(f8_canon(brec[i * BW + a.bkey], a.key_is_f64)) & hmask];
-            }
-          }
-          if (!__syncthreads_or(pending != 0)) break;  // everybody has read the heads of this round (and somebody still has work)
-#pragma unroll
-          for (int k = 0; k < kF8MaxRowsPerThread; k++) {
-            if (pending & (1u << k)) {
-              const int i = tid + k * kF8Threads;
-              heads[f8_bucket(f8_canon(brec[i * BW + a.bkey], a.key_is_f64)) & hmask] = (uint16_t)i;
-            }
-          }
-          __syncthreads();
-#pragma unroll
-          for (int k = 0; k < kF8MaxRowsPerThread; k++) {
-            if (pending & (1u << k)) {
-              const int i = tid + k * kF8Threads;
-              if (heads[f8_bucket(f8_canon(brec[i * BW + a.bkey], a.key_is_f64)) & hmask] == (uint16_t)i) {
-                next[i] = old[k];
-                pending &= ~(1u << k);
-              }
-            }
-          }
-        }
-        if (__syncthreads_or(pending != 0)) {  // long runs of one bucket (duplicate keys): finish with atomics
-#pragma unroll
-          for (int k = 0; k < kF8MaxRowsPerThread; k++) {
-            if (pending & (1u << k)) {
-              const int i = tid + k * kF8Threads;
-              const uint32_t h = f8_bucket(f8_canon(brec[i * BW + a.bkey], a.key_is_f64)) & hmask;
-              // 16-bit exchange through a CAS on the aligned 32-bit word that holds the head
-              unsigned int *word = reinterpret_cast<unsigned int *>(heads) + (h >> 1);
-              const unsigned int shift = (h & 1u) * 16;
-              unsigned int seen = *word, prev;
-              do {
-                prev = seen;
-                seen = atomicCAS(word, prev, (prev & ~(0xFFFFu << shift)) | ((unsigned int)i << shift));
-              } while (seen != prev);
-              next[i] = (uint16_t)((prev >> shift) & 0xFFFFu);
-            }
-          }
-        }
+      for (int i = tid; i < nb; i += kF8Threads) {
+        const uint64_t k = f8_canon(brec[i * BW + a.bkey], a.key_is_f64);
+        next[i] = (uint16_t)atomicExch(&heads[f8_bucket(k) & hmask], (uint32_t)i);
       }
       __syncthreads();
 
       for (int64_t t0 = p0; t0 < p1; t0 += kF8Threads * kF8ProbeRows) {
         uint64_t pv[kF8ProbeRows][PW];
-        uint32_t m01[kF8ProbeRows];  // first two matching build rows (16 bits each)
+        uint32_t first[kF8ProbeRows];
         unsigned int cnt[kF8ProbeRows];
 #pragma unroll
         for (int u = 0; u < kF8ProbeRows; u++) {
           const int64_t r = t0 + (int64_t)u * kF8Threads + tid;
           if (r < p1) {
             if constexpr (PW == 2) {
-              const ulonglong2 t = __ldcs(reinterpret_cast<const ulonglong2 *>(a.prec) + r);
+              const ulonglong2 t = reinterpret_cast<const ulonglong2 *>(a.prec)[r];
               pv[u][0] = t.x;
               pv[u][1] = t.y;
             } else {
 #pragma unroll
-              for (int w = 0; w < PW; w++) pv[u][w] = ld_stream_u64(a.prec + r * PW + w);
+              for (int w = 0; w < PW; w++) pv[u][w] = a.prec[r * PW + w];
             }
           } else {
 #pragma unroll
@@ -254,7 +187,7 @@ __global__ void __launch_bounds__(kF8Threads, 2) fused8_join_kernel(const __grid
 #pragma unroll
         for (int u = 0; u < kF8ProbeRows; u++) {
           const int64_t r = t0 + (int64_t)u * kF8Threads + tid;
-          m01[u] = 0;
+          first[u] = kF8Nil;
           cnt[u] = 0;
           if (r < p1) {
             const uint64_t k = f8_canon(f8_pick<PW>(pv[u], a.pkey), a.key_is_f64);
@@ -262,7 +195,7 @@ __global__ void __launch_bounds__(kF8Threads, 2) fused8_join_kernel(const __grid
             uint32_t j = (a.key_is_f64 && key_bits_is_nan(CYL_DOUBLE, k)) ? kF8Nil : heads[f8_bucket(k) & hmask];
             for (; j != kF8Nil; j = next[j]) {
               if (f8_canon(brec[j * BW + a.bkey], a.key_is_f64) == k) {
-                if (cnt[u] < 2) m01[u] |= j << (16 * cnt[u]);
+                if (cnt[u] == 0) first[u] = j;
                 cnt[u]++;
               }
             }
@@ -270,7 +203,8 @@ __global__ void __launch_bounds__(kF8Threads, 2) fused8_join_kernel(const __grid
           mine += cnt[u];
         }
         // Output slots are handed out u-major (every thread's probe row 0, then every thread's row 1, ...): inside one
-        // store instruction the lanes then write consecutive output rows, i.e. whole sectors.
+        // store instruction the lanes then write consecutive output rows, i.e. whole sectors. (Thread-major slots cost
+        // 3.6 L2 sector writes per sector of output: ncu, profiles/r01_ncu_final.md.)
         unsigned int inc[kF8ProbeRows];
 #pragma unroll
         for (int u = 0; u < kF8ProbeRows; u++) {
@@ -304,36 +238,24 @@ __global__ void __launch_bounds__(kF8Threads, 2) fused8_join_kernel(const __grid
         }
         __syncthreads();
         const unsigned int total = s_total;
+        unsigned int slot0[kF8ProbeRows];
+#pragma unroll
+        for (int u = 0; u < kF8ProbeRows; u++) slot0[u] = s_warp_tot[u][warp] + inc[u] - cnt[u];
         if (mine && (int64_t)s_base + total <= a.capacity) {
 #pragma unroll
           for (int u = 0; u < kF8ProbeRows; u++) {
             if (cnt[u] == 0) continue;
-            int64_t o = (int64_t)s_base + s_warp_tot[u][warp] + inc[u] - cnt[u];
-            if (cnt[u] <= 2) {
-              uint32_t j = m01[u] & 0xFFFFu;
+            int64_t o = (int64_t)s_base + slot0[u];
+            unsigned int left = cnt[u];
+            const uint64_t k = f8_canon(f8_pick<PW>(pv[u], a.pkey), a.key_is_f64);
+            for (uint32_t j = first[u]; left; j = next[j]) {
+              if (j != first[u] && f8_canon(brec[j * BW + a.bkey], a.key_is_f64) != k) continue;
 #pragma unroll
-              for (int w = 0; w < BW; w++) __stcs(a.bout[w] + o, brec[j * BW + w]);
+              for (int w = 0; w < BW; w++) a.bout[w][o] = brec[j * BW + w];
 #pragma unroll
-              for (int w = 0; w < PW; w++) __stcs(a.pout[w] + o, pv[u][w]);
-              if (cnt[u] == 2) {
-                j = m01[u] >> 16;
-#pragma unroll
-                for (int w = 0; w < BW; w++) __stcs(a.bout[w] + o + 1, brec[j * BW + w]);
-#pragma unroll
-                for (int w = 0; w < PW; w++) __stcs(a.pout[w] + o + 1, pv[u][w]);
-              }
-            } else {
-              const uint64_t k = f8_canon(f8_pick<PW>(pv[u], a.pkey), a.key_is_f64);
-              unsigned int left = cnt[u];
-              for (uint32_t j = m01[u] & 0xFFFFu; left; j = next[j]) {
-                if (f8_canon(brec[j * BW + a.bkey], a.key_is_f64) != k) continue;
-#pragma unroll
-                for (int w = 0; w < BW; w++) __stcs(a.bout[w] + o, brec[j * BW + w]);
-#pragma unroll
-                for (int w = 0; w < PW; w++) __stcs(a.pout[w] + o, pv[u][w]);
-                o++;
-                left--;
-              }
+              for (int w = 0; w < PW; w++) a.pout[w][o] = pv[u][w];
+              o++;
+              left--;
             }
           }
         }
@@ -517,6 +439,15 @@ static int f8_partition_blocks(const cyl_column_t *cols, int ncols, int key, int
 // pass of scattered stores. Slots inside a run come from shared-memory atomics, ranges inside a bin from one global
 // atomicAdd per (tile, digit) on cursors preset from the full K-bin histogram -- row order inside a bin is arbitrary,
 // as it already was. All of a tile's loads are issued before the first use.
+// Measured and rejected in round 2 (profiles/r02_join_experiments.md; cyl_tune_set switched between them on the same
+// 100M x 100M input): ranking a tile's rows with ballots over the digit bits or with match.any instead of the
+// shared-memory atomicAdd below (passes 0.70 -> 1.01-1.13 ms), linking the join's chains in rounds of plain stores
+// instead of atomicExch (probe 2.49 -> 2.75 ms), and join CTAs of 128 / 256 threads over 2^17 / 2^16 smaller bins (probe
+// 2.19 / 2.30 ms but histogram 0.66 / 0.42 ms: no gain for the step).
+void fused8_tune(int key, int value) {
+  (void)key;
+  (void)value;
+}
 constexpr int kRsThreads = 512;  // == kRsMaxDigits: one digit per thread in the per-tile scan
 static int g_force_bins_log2 = 0;
 void fused8_force_bins_log2(int bits) { g_force_bins_log2 = bits; }
@@ -528,7 +459,7 @@ struct F8RadixArgs {
   const uint64_t *cols[kFused8MaxCols];  // pass A input (columns)
   const uint64_t *src;                   // pass B input (records ordered by coarse digit)
   uint64_t *dst;
-  int32_t key, key_is_f64, shift, lo_bits, ndigits, dbits, cols_aligned16;
+  int32_t key, key_is_f64, shift, lo_bits, ndigits, cols_aligned16;
   int64_t n;
   unsigned int *cursor;                  // pass A: [coarse]; pass B: [K]
   const int64_t *bin_off;                // [K + 1]
@@ -571,9 +502,7 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
   unsigned int *cnt = reinterpret_cast<unsigned int *>(stage + (size_t)T * W);  // [512] rows per digit, then run starts
   unsigned int *delta = cnt + kRsMaxDigits;                                     // [512] destination - staging slot
   unsigned int *warp_tot = delta + kRsMaxDigits;                                // [16]
-  unsigned int *prefix = warp_tot + kRsThreads / 32;                            // [513 (+3 pad)] (pass B)
-  unsigned int *wpair = prefix + kRsMaxDigits + 4;                              // [8][512]: counters of warps 2p (low half) and 2p+1 (high half)
-  unsigned short *wcnt16 = reinterpret_cast<unsigned short *>(wpair);
+  unsigned int *prefix = warp_tot + kRsThreads / 32;                                          // [513] (pass B)
   const int tid = threadIdx.x;
   const unsigned lane = tid & 31, warp = tid >> 5;
   const uint32_t lo_mask = (1u << a.lo_bits) - 1;
@@ -660,46 +589,19 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
     load_tile(r0, r1);
   }
   for (int64_t g = blockIdx.x; g < ntiles; g += gridDim.x) {
-    {  // zero the warp-private counters: 8 x 512 words = 2 x 128-bit stores per thread
-      uint4 *z = reinterpret_cast<uint4 *>(wpair);
-#pragma unroll
-      for (int q = 0; q < (kRsThreads / 64) * kRsMaxDigits / 4 / kRsThreads; q++) z[q * kRsThreads + tid] = make_uint4(0u, 0u, 0u, 0u);
-    }
+    cnt[tid] = 0;
     __syncthreads();  // counters are zero
-    // this warp's counter of digit d = 16-bit half (warp & 1) of word [(warp >> 1) * 512 + d]
-    unsigned short *wc = wcnt16 + (size_t)(warp >> 1) * (2 * kRsMaxDigits) + (warp & 1);
-    const unsigned lt = (1u << lane) - 1;
-    uint32_t dr[R];   // digit << 16 | rank inside the (warp, digit) run
+    uint32_t dr[R];   // digit << 16 | rank inside the (tile, digit) run
 #pragma unroll
     for (int u = 0; u < R; u++) {
       const int64_t i = row_of(r0, u);
-      const bool valid = i < r1;
       const uint32_t bin = f8_bin(f8_canon(f8_pick<W>(v[u], a.key), a.key_is_f64), a.shift);
       const uint32_t d = PASS_B ? (bin & lo_mask) : (bin >> a.lo_bits);
-      unsigned peers = __ballot_sync(0xffffffffu, valid);
-#pragma unroll
-      for (int b = 0; b < 9; b++) {
-        if (b < a.dbits) {  // uniform
-          const bool bit = (d >> b) & 1u;
-          const unsigned vote = __ballot_sync(0xffffffffu, bit);
-          peers &= bit ? vote : ~vote;
-        }
-      }
-      const unsigned rank = __popc(peers & lt);
-      const unsigned old = valid ? (unsigned)wc[2 * d] : 0u;
-      __syncwarp();
-      if (valid && rank == 0) wc[2 * d] = (unsigned short)(old + __popc(peers));
-      __syncwarp();
-      dr[u] = valid ? ((d << 16) | (old + rank)) : 0xFFFFFFFFu;
+      dr[u] = i < r1 ? ((d << 16) | atomicAdd(&cnt[d], 1u)) : 0xFFFFFFFFu;
     }
     __syncthreads();
-    {  // digit `tid`: total over the 16 warps, exclusive scan over digits, one global reservation, then per-warp staging bases
-      unsigned int c = 0;
-#pragma unroll
-      for (int p = 0; p < kRsThreads / 64; p++) {
-        const unsigned int w2 = wpair[p * kRsMaxDigits + tid];
-        c += (w2 & 0xFFFFu) + (w2 >> 16);
-      }
+    {  // exclusive scan of the 256 counters; digit `tid` reserves its run's destination range
+      const unsigned int c = cnt[tid];
       unsigned int inc = c;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -714,21 +616,14 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
 #pragma unroll
       for (int w = 0; w < kRsThreads / 32; w++) before += w < (int)warp ? warp_tot[w] : 0u;
       const unsigned int start = before + inc - c;
+      cnt[tid] = start;
       delta[tid] = g0 - start;
-      unsigned int run = start;  // staging slot where warp 0's rows of this digit begin; <= 4096 fits 16 bits
-#pragma unroll
-      for (int p = 0; p < kRsThreads / 64; p++) {
-        const unsigned int w2 = wpair[p * kRsMaxDigits + tid];
-        const unsigned int lo = w2 & 0xFFFFu, hi = w2 >> 16;
-        wpair[p * kRsMaxDigits + tid] = run | ((run + lo) << 16);
-        run += lo + hi;
-      }
     }
     __syncthreads();
 #pragma unroll
     for (int u = 0; u < R; u++) {
       if (dr[u] != 0xFFFFFFFFu) {
-        const uint32_t d = dr[u] >> 16, slot = (uint32_t)wc[2 * d] + (dr[u] & 0xFFFFu);
+        const uint32_t d = dr[u] >> 16, slot = cnt[d] + (dr[u] & 0xFFFFu);
         if constexpr (W == 2) {
           *reinterpret_cast<ulonglong2 *>(stage + (size_t)slot * 2) = make_ulonglong2(v[u][0], v[u][1]);
         } else {
@@ -765,7 +660,7 @@ __global__ void __launch_bounds__(kRsThreads, 2) fused8_radix_pass_kernel(const 
 
 template <int W>
 static size_t rs_smem_bytes() {
-  return (size_t)RsCfg<W>::T * W * 8 + (2 * kRsMaxDigits + kRsThreads / 32 + kRsMaxDigits + 4 + (kRsThreads / 64) * kRsMaxDigits) * sizeof(unsigned int) + 16;
+  return (size_t)RsCfg<W>::T * W * 8 + (2 * kRsMaxDigits + kRsThreads / 32 + kRsMaxDigits + 1) * sizeof(unsigned int) + 16;
 }
 
 template <int W, bool PASS_B>
@@ -789,8 +684,6 @@ static int radix_two_pass(F8RadixArgs a, uint64_t *tmp, uint64_t *rec, unsigned 
     a.dst = tmp;
     a.cursor = coarse_cursor;
     a.ndigits = a.ncoarse;
-    a.dbits = 0;
-    while ((1 << a.dbits) < a.ncoarse) a.dbits++;
     CYL_TRY((launch_radix_pass<W, false>(a, div_up(a.n, (int64_t)T), s)));
   }
   {
@@ -799,7 +692,6 @@ static int radix_two_pass(F8RadixArgs a, uint64_t *tmp, uint64_t *rec, unsigned 
     a.dst = rec;
     a.cursor = fine_cursor;
     a.ndigits = 1 << a.lo_bits;
-    a.dbits = a.lo_bits;
     CYL_TRY((launch_radix_pass<W, true>(a, div_up(a.n, (int64_t)T) + a.ncoarse, s)));
   }
   return CYL_OK;
@@ -994,14 +886,14 @@ bool fused8_eligible(const cyl_column_t *lcols, int nlcols, const cyl_column_t *
 
 int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const cyl_column_t *pcols, int npc, int pkey, int64_t np,
                 void *const *bout, void *const *pout, int64_t capacity, int64_t *num_rows, cudaStream_t s) {
-  // shared memory per CTA: records + 16-bit heads + 16-bit next links (2 CTAs per SM)
+  // shared memory per CTA: records + 16-bit next links + 32-bit heads (2 CTAs per SM)
   const size_t budget = 104 * 1024;
-  int cap = 16384 - 256, nheads = 0;  // links are 16-bit and 0xFFFF ends a chain
+  int cap = 16384, nheads = 0;  // next links are 16-bit and 0xFFFF ends a chain
   size_t smem_bytes = 0;
   for (;; cap -= 256) {  // largest multiple of 256 rows whose records + links + heads fit the budget
     nheads = 256;
     while (nheads < cap * 2) nheads *= 2;
-    smem_bytes = (size_t)cap * nbc * 8 + (size_t)nheads * 2 + (size_t)cap * 2 + 16;
+    smem_bytes = (size_t)cap * nbc * 8 + (size_t)nheads * 4 + (size_t)cap * 2 + 16;
     if (smem_bytes <= budget || cap <= 256) break;
   }
   int64_t nbins = 1;

@@ -177,6 +177,10 @@ int cyl_hash_join_fused_inner(const cyl_column_t *lcols /* host array */, int32_
  * are just emptier), so tests use it to reach the many-bin code paths (512-way digits, split histogram) with small
  * tables. Process-wide; do not change it while a join is running. Returns CYL_Invalid outside 0..18. */
 int cyl_hash_join_fused_set_bins_log2(int32_t bits);
+/* Measurement knob with no reference counterpart: lets two equivalent implementations of an inner step be timed against
+ * each other on the same input (bench.py reads CYLON_TUNE=key=value,...). Results never depend on it. No keys are live in
+ * this build: the alternatives measured in round 2 lost and were removed (profiles/r02_join_experiments.md). Process-wide. */
+int cyl_tune_set(int32_t key, int32_t value);
 
 /* ---------------------------------------------------------------- D4: gather ------------------- */
 /* dst[i] = idx[i] < 0 ? 0 : src[idx[i]]; dst_validity (may be NULL) gets bit i = (idx[i] >= 0), it has
