@@ -308,6 +308,34 @@ def aggregate(col, gid_buf, num_groups, op, stream=None):
     return out.to_numpy(dt, num_groups)
 
 
+def groupby_fused(key, values, agg_value, agg_op, capacity=None, stream=None):
+    """cyl_groupby_fused through the C-ABI -> (key ndarray, [aggregate ndarrays], groups, attempts); None if unsupported."""
+    av = (C.c_int32 * len(agg_value))(*agg_value)
+    ao = (C.c_int32 * len(agg_op))(*agg_op)
+    kc = key.c_struct()
+    if not lib().cyl_groupby_fused_supported(C.byref(kc), c_columns(values), len(values), av, ao, len(agg_op)):
+        return None
+    n = key.length
+    if capacity is None:
+        capacity = max(1, min(n, n // 4 + (1 << 20)))
+    attempts = 0
+    while True:
+        attempts += 1
+        out_key = DeviceBuffer(8 * max(1, capacity))
+        outs = [DeviceBuffer(8 * max(1, capacity)) for _ in agg_op]
+        ptrs = (C.c_void_p * len(outs))(*[o.ptr for o in outs])
+        g = C.c_int64()
+        check(lib().cyl_groupby_fused(C.byref(kc), c_columns(values), len(values), av, ao, len(agg_op), C.c_int64(capacity), _p(out_key), ptrs,
+                                      C.byref(g), C.c_void_p(stream)))
+        if g.value <= capacity:
+            aggs = []
+            for a, o in enumerate(outs):
+                dt = np.dtype("int64") if agg_op[a] == COUNT else TYPE2NP[values[agg_value[a]].type]
+                aggs.append(o.to_numpy(dt, g.value))
+            return out_key.to_numpy(TYPE2NP[key.type], g.value), aggs, g.value, attempts
+        capacity = g.value
+
+
 def rowset_mask(lcols, rcols, op, stream=None):
     nl = lcols[0].length
     nr = rcols[0].length if rcols else 0

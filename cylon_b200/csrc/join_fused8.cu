@@ -805,8 +805,8 @@ static int f8_partition_two_pass(const cyl_column_t *cols, int ncols, int key, i
   }
 }
 
-static int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_t nbins, int shift, uint64_t *rec, int64_t *bin_off,
-                        cudaStream_t s) {
+int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_t nbins, int shift, uint64_t *rec, int64_t *bin_off,
+                 cudaStream_t s) {
   // Measured on B200 at 100M rows x 32768 bins (profiles/r01_fused_join_notes.md): block-private cursors make the
   // scatter SLOWER (4.4 ms vs 2.9 ms) because 148 CTAs x 32768 bins leave ~5M partially written lines in flight, far
   // more than L2 can hold until they fill; shared global cursors keep only K write frontiers alive. A two-level split

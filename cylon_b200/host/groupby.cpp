@@ -26,6 +26,55 @@ Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_
   void *stream = ctx->GetStream();
   const int64_t n = table->Rows();
 
+  // fast path: one 8-byte key, 8-byte numeric values -> groups and all aggregates in one sweep (groupby_fused8.cu)
+  if (idx_cols.size() == 1 && ctx->GetConfig("cylon.groupby.fused", "1") != "0") {
+    const cyl_column_t key = table->GetColumn(idx_cols[0])->desc();
+    std::vector<cyl_column_t> values;  // distinct source columns (the same column may feed several aggregates)
+    std::vector<int32_t> agg_value, agg_op;
+    for (const auto &a : aggregations) {
+      const cyl_column_t d = table->GetColumn(a.first)->desc();
+      int32_t at = -1;
+      for (size_t v = 0; v < values.size(); v++)
+        if (values[v].data == d.data && values[v].type == d.type) at = (int32_t)v;
+      if (at < 0) {
+        values.push_back(d);
+        at = (int32_t)values.size() - 1;
+      }
+      agg_value.push_back(at);
+      agg_op.push_back(a.second == compute::SUM ? CYL_AGG_SUM : a.second == compute::MIN ? CYL_AGG_MIN : a.second == compute::MAX ? CYL_AGG_MAX : CYL_AGG_COUNT);
+    }
+    if (n > 0 && cyl_groupby_fused_supported(&key, values.data(), (int32_t)values.size(), agg_value.data(), agg_op.data(), (int32_t)agg_op.size())) {
+      int64_t capacity = std::min<int64_t>(n, n / 4 + (1 << 20));
+      for (int attempt = 0; attempt < 2; attempt++) {
+        std::vector<std::shared_ptr<Column>> cols;
+        std::shared_ptr<Column> kc;
+        const auto &ksrc = table->GetColumn(idx_cols[0]);
+        RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(ksrc->name(), ksrc->type(), 8, capacity, capacity * 8, false, stream, &kc));
+        cols.push_back(kc);
+        std::vector<void *> outs;
+        for (const auto &a : aggregations) {
+          const auto &src = table->GetColumn(a.first);
+          const int32_t type = a.second == compute::COUNT ? (int32_t)CYL_INT64 : src->type();
+          std::shared_ptr<Column> col;
+          RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(std::string(compute::AggregationPrefix(a.second)) + src->name(), type, 8, capacity, capacity * 8,
+                                                         false, stream, &col));
+          outs.push_back(col->mutable_data());
+          cols.push_back(col);
+        }
+        int64_t groups = 0;
+        CYL_RETURN_IF_FAILED(cyl_groupby_fused(&key, values.data(), (int32_t)values.size(), agg_value.data(), agg_op.data(), (int32_t)agg_op.size(),
+                                               capacity, kc->mutable_data(), outs.data(), &groups, stream));
+        if (groups <= capacity) {
+          for (auto &c : cols) c->truncate(groups);
+          output = std::make_shared<Table>(std::move(cols), ctx);
+          return Status::OK();
+        }
+        capacity = groups;  // the optimistic capacity was too small: the exact count is known now
+      }
+      return Status(Code::ExecutionError, "fused group-by did not fit its exact capacity");
+    }
+  }
+
   // make_groups (hash_groupby.cpp:92-126)
   detail::DevBuf gid, first;
   RETURN_CYLON_STATUS_IF_FAILED(gid.alloc((size_t)(n + 1) * 8, stream));
@@ -89,7 +138,29 @@ Status DistributedHashGroupBy(std::shared_ptr<Table> &table, const std::vector<i
   for (size_t i = 0; i < aggregate_cols.size(); i++) aggs.emplace_back((int32_t)(index_cols.size() + i), aggregate_ops[i]);
 
   const int world = table->GetContext()->GetWorldSize();
+  for (auto op : aggregate_ops)  // refuse before anything is shuffled (the reference finds out after its shuffle, hash_groupby.cpp:217-248)
+    if (op != compute::SUM && op != compute::MIN && op != compute::MAX && op != compute::COUNT)
+      return Status(Code::NotImplemented, "DistributedHashGroupBy: only SUM/MIN/MAX/COUNT run on the GPU path");
   std::shared_ptr<Table> local;
+  if (world > 1 && !is_associative(aggregate_ops) && table->GetContext()->GetConfig("cylon.groupby.preaggregate", "1") != "0") {
+    // COUNT among the operations. The reference then ships every raw row through the shuffle (groupby.cpp:60-77: it only
+    // pre-aggregates when all operations are in {SUM, MIN, MAX}). Here the rows are still reduced locally first and the
+    // partial COUNTs are SUMmed after the shuffle, so only one row per (rank, group) crosses NVLink; the result columns
+    // get the names the reference's single application produces (count_x, not sum_count_x). Values are identical except
+    // for the association order of floating-point SUMs (two levels instead of one; within the 1e-12 tolerance).
+    RETURN_CYLON_STATUS_IF_FAILED(HashGroupBy(projected, idx_after, aggs, local));
+    std::shared_ptr<Table> shuffled;
+    std::vector<int> hc(idx_after.begin(), idx_after.end());
+    RETURN_CYLON_STATUS_IF_FAILED(Shuffle(local, hc, shuffled));
+    std::vector<std::pair<int32_t, compute::AggregationOpId>> combine;
+    for (size_t i = 0; i < aggregate_ops.size(); i++)
+      combine.emplace_back((int32_t)(index_cols.size() + i), aggregate_ops[i] == compute::COUNT ? compute::SUM : aggregate_ops[i]);
+    RETURN_CYLON_STATUS_IF_FAILED(HashGroupBy(shuffled, idx_after, combine, output));
+    for (size_t i = 0; i < aggregate_ops.size(); i++)
+      output->GetColumn((int)(index_cols.size() + i))
+          ->set_name(std::string(compute::AggregationPrefix(aggregate_ops[i])) + projected->GetColumn((int)(index_cols.size() + i))->name());
+    return Status::OK();
+  }
   if (world == 1 || is_associative(aggregate_ops)) {  // groupby.cpp:60-64
     RETURN_CYLON_STATUS_IF_FAILED(HashGroupBy(projected, idx_after, aggs, local));
   } else {

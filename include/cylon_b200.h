@@ -216,6 +216,20 @@ int cyl_groupby_hash(const cyl_column_t *keys /* host array */, int32_t nkeys, i
  * (DBL_MIN/FLT_MIN for floating point -- the reference's behaviour). col is a host pointer to one descriptor.
  * Replaces aggregate<op,T> (groupby/hash_groupby.cpp:142-201) + compute/aggregate_kernels.hpp:410-485. */
 int cyl_aggregate(const cyl_column_t *col /* host */, const int64_t *gid, int64_t num_groups, int32_t op, void *out, void *stream);
+/* Fused fast path of HashGroupBy for ONE 8-byte key column (int64 / uint64 / double / date64 / timestamp / time64) and 8-byte
+ * value columns (int64 / uint64 / double), all without validity bitmaps, at most 3 distinct value columns and 4 aggregates:
+ * make_groups + every aggregate in one sweep (rows radix-partitioned on the key hash, one CTA per bin with its group table
+ * in shared memory). agg_value[a] indexes `values`, agg_op[a] is a cyl_agg_op_t. out_key and out_aggs[a] are device
+ * buffers of `capacity` 8-byte values (COUNT writes int64). *num_groups (host out; the call synchronises) always
+ * receives the exact number of groups; the outputs were written only if it is <= capacity, otherwise repeat the call
+ * with capacity >= *num_groups. Group order is unspecified (the reference numbers groups in first-seen order); SUM of
+ * doubles adds in an unspecified order (within the 1e-12 relative tolerance of BASELINE.json, not bit for bit).
+ * Replaces make_groups + aggregate<op,T> (groupby/hash_groupby.cpp:92-201) + compute/aggregate_kernels.hpp:410-485. */
+int cyl_groupby_fused_supported(const cyl_column_t *key /* host */, const cyl_column_t *values /* host array */, int32_t nvalues,
+                                const int32_t *agg_value, const int32_t *agg_op, int32_t naggs);
+int cyl_groupby_fused(const cyl_column_t *key /* host */, const cyl_column_t *values /* host array */, int32_t nvalues, const int32_t *agg_value,
+                      const int32_t *agg_op, int32_t naggs, int64_t capacity, void *out_key, void *const *out_aggs /* host array */,
+                      int64_t *num_groups /* host out */, void *stream);
 
 /* ---------------------------------------------------------------- E: set operations / unique --- */
 /* One byte per row: mask_l[i] / mask_r[j] = 1 when the row belongs to the result.
