@@ -26,8 +26,17 @@
 
 namespace cylb {
 
-constexpr int kGbThreads = 1024;
-constexpr int kGbSlots = 4096;      // power of two; a bin is sized to <= ~2000 rows on average, so load stays below 0.6
+// Several small CTAs per SM rather than one large one: a bin is a short job (load its rows, two passes, write its groups),
+// each step waiting on the one before, so a single 1024-thread CTA per SM spent most of its time in exposed latencies
+// (6 ms for 125M rows); 256 threads and a 1024-slot table leave room for 4-5 CTAs per SM whose phases overlap.
+static int g_gb_threads = 256;  // CTA size (cyl_tune_set key 6): 256 / 512 / 1024
+static int g_gb_bins_log2 = 0;  // > 0: force 2^bits bins (key 8)
+static int g_gb_slots = 1024;   // table slots, a power of two (key 7); bins average 0.47 * slots rows, so load stays below 0.6
+void groupby_fused8_tune(int key, int value) {
+  if (key == 6) g_gb_threads = value;
+  if (key == 7) g_gb_slots = value;
+  if (key == 8) g_gb_bins_log2 = value;
+}
 constexpr int kGbMaxAggs = 4;
 constexpr unsigned long long kGbEmpty = 0xFFFFFFFFFFFFFFFFull;
 
@@ -49,6 +58,7 @@ struct GbArgs {
   unsigned long long *out_cursor;  // groups written so far (exact count even when capacity is exceeded)
   unsigned int *work_counter;
   int *overflow;                   // set when a bin held more groups than the table has slots
+  int32_t slots;                   // table slots (power of two)
 };
 
 // order-preserving map of an 8-byte value onto unsigned 64-bit
@@ -78,142 +88,284 @@ __device__ __forceinline__ uint64_t gb_pick(const uint64_t (&v)[W], int idx) {
   return r;
 }
 
-template <int W>
-__global__ void __launch_bounds__(kGbThreads, 1) groupby_fused8_kernel(const __grid_constant__ GbArgs a) {
+// Folds a combined contribution `c` (already encoded for MIN / MAX) into a shared-memory state word that other warps may
+// be updating too.
+__device__ __forceinline__ void gb_update_enc(unsigned long long *st, int op, unsigned long long c) {
+  if (op == GB_COUNT || op == GB_SUM_INT) {
+    atomicAdd(st, c);
+  } else if (op == GB_SUM_F64) {
+    const double x = __longlong_as_double((long long)c);
+    unsigned long long seen = *st, prev;
+    do {
+      prev = seen;
+      seen = atomicCAS(st, prev, (unsigned long long)__double_as_longlong(__longlong_as_double((long long)prev) + x));
+    } while (seen != prev);
+  } else {
+    unsigned long long seen = *st;
+    while (op == GB_MIN ? c < seen : c > seen) {  // only a better value ever reaches the atomic
+      const unsigned long long prev = atomicCAS(st, seen, c);
+      if (prev == seen) break;
+      seen = prev;
+    }
+  }
+}
+
+// folds one replica's state word into an accumulator of the same aggregate
+__device__ __forceinline__ unsigned long long gb_merge(unsigned long long acc, unsigned long long w, int op) {
+  if (op == GB_SUM_F64) return (unsigned long long)__double_as_longlong(__longlong_as_double((long long)acc) + __longlong_as_double((long long)w));
+  if (op == GB_MIN) return w < acc ? w : acc;
+  if (op == GB_MAX) return w > acc ? w : acc;
+  return acc + w;  // COUNT, integer SUM (wraps)
+}
+
+constexpr int kGbKeep = 4;  // rows per thread whose record and slot stay in registers between the two passes over a bin
+
+// Two passes over a bin. Pass 1 claims a slot and a dense group id for every distinct key. Pass 2 folds the rows into
+// state words indexed by (replica, group id): the bin's ng groups are replicated R = min(32, slots / ng) times and warp w
+// updates replica w mod R, so a bin with few groups (config 4: ~15 per bin, ~125 rows each) does not serialise 1024
+// threads on 15 addresses -- measured 15.8 ms for 125M rows with one copy per group; the replicas are merged when the
+// groups are written out.
+template <int W, int kGbThreads>
+__global__ void __launch_bounds__(kGbThreads, 1024 / kGbThreads) groupby_fused8_kernel(const __grid_constant__ GbArgs a) {
+  const int kGbSlots = a.slots;
   extern __shared__ __align__(16) unsigned char gb_smem[];
-  unsigned long long *keys = reinterpret_cast<unsigned long long *>(gb_smem);   // [kGbSlots + 1] (+1: the key equal to kGbEmpty)
-  unsigned long long *state = keys + kGbSlots + 2;                              // [naggs][kGbSlots + 2]
-  unsigned short *list = reinterpret_cast<unsigned short *>(state + (size_t)a.naggs * (kGbSlots + 2));  // [kGbSlots + 1] occupied slots
-  __shared__ unsigned int s_bin, s_ngroups, s_special;
+  unsigned long long *keys = reinterpret_cast<unsigned long long *>(gb_smem);   // [kGbSlots + 2]; slot kGbSlots serves the key equal to kGbEmpty
+  unsigned long long *state = keys + kGbSlots + 2;                              // [naggs][kGbSlots]: entry replica * ng + gid
+  unsigned short *gid_of = reinterpret_cast<unsigned short *>(state + (size_t)a.naggs * kGbSlots);  // [kGbSlots + 2] slot -> group id
+  unsigned short *slot_of = gid_of + kGbSlots + 2;                                                  // [kGbSlots + 2] group id -> slot
+  unsigned int *locks = reinterpret_cast<unsigned int *>(slot_of + kGbSlots + 2);                   // [kGbSlots] one per state entry
+  __shared__ unsigned int s_bin, s_ng, s_special;
   __shared__ unsigned long long s_base;
   const int tid = threadIdx.x;
-  constexpr int STRIDE = kGbSlots + 2;
+  const unsigned int warp = tid >> 5;
 
-  // the table starts clean and every bin leaves it clean (its emit phase resets exactly the slots it used)
+  // the table starts clean and every bin leaves it clean (its emit phase resets exactly what it used)
   for (int i = tid; i < kGbSlots + 1; i += kGbThreads) keys[i] = kGbEmpty;
   for (int ag = 0; ag < a.naggs; ag++)
-    for (int i = tid; i < kGbSlots + 1; i += kGbThreads) state[ag * STRIDE + i] = a.init[ag];
+    for (int i = tid; i < kGbSlots; i += kGbThreads) state[ag * kGbSlots + i] = a.init[ag];
+  for (int i = tid; i < kGbSlots; i += kGbThreads) locks[i] = 0u;
   if (tid == 0) {
-    s_ngroups = 0;
+    s_ng = 0;
     s_special = 0;
   }
 
+  auto load_row = [&](int64_t r, uint64_t (&v)[W]) {
+    if constexpr (W == 2) {
+      const ulonglong2 t = *(reinterpret_cast<const ulonglong2 *>(a.rec) + r);
+      v[0] = t.x;
+      v[1] = t.y;
+    } else if constexpr (W == 4) {
+      const ulonglong2 t0 = *reinterpret_cast<const ulonglong2 *>(a.rec + r * 4);
+      const ulonglong2 t1 = *reinterpret_cast<const ulonglong2 *>(a.rec + r * 4 + 2);
+      v[0] = t0.x; v[1] = t0.y; v[2] = t1.x; v[3] = t1.y;
+    } else {
+#pragma unroll
+      for (int w = 0; w < W; w++) v[w] = a.rec[r * W + w];
+    }
+  };
+  // slot of `key`; claim == true may insert it (and then assigns the next group id)
+  auto find_slot = [&](unsigned long long key, bool claim) -> int {
+    if (key == kGbEmpty) {
+      if (claim && atomicCAS(&s_special, 0u, 1u) == 0u) {
+        const unsigned int g = atomicAdd(&s_ng, 1u);
+        gid_of[kGbSlots] = (unsigned short)g;
+        slot_of[g] = (unsigned short)kGbSlots;
+      }
+      return kGbSlots;
+    }
+    unsigned int h = (unsigned int)((key * 0x9E3779B97F4A7C15ULL) >> 40) & (kGbSlots - 1);
+    for (int probes = 0; probes < kGbSlots; probes++) {
+      unsigned long long cur = keys[h];
+      if (cur == kGbEmpty && claim) {
+        cur = atomicCAS(&keys[h], kGbEmpty, key);
+        if (cur == kGbEmpty) {  // this thread inserted the key: it names the group
+          const unsigned int g = atomicAdd(&s_ng, 1u);
+          gid_of[h] = (unsigned short)g;
+          slot_of[g] = (unsigned short)h;
+          return (int)h;
+        }
+      }
+      if (cur == key) return (int)h;
+      if (cur == kGbEmpty) return -1;
+      h = (h + 1) & (kGbSlots - 1);
+    }
+    return -1;
+  };
+
+  if (tid == 0) s_bin = atomicAdd(a.work_counter, 1u);
   while (true) {
-    __syncthreads();
-    if (tid == 0) s_bin = atomicAdd(a.work_counter, 1u);
     __syncthreads();
     const int64_t bin = s_bin;
     if (bin >= a.nbins) break;
+    // the next bin is requested now and the answer stored at the end of this one: its latency hides behind the work
+    unsigned int next_bin = 0;
+    if (tid == 0) next_bin = atomicAdd(a.work_counter, 1u);
     const int64_t r0 = a.bin_off[bin], r1 = a.bin_off[bin + 1];
-    if (r1 == r0) continue;
+    unsigned long long base_reg = 0;
 
-    for (int64_t r = r0 + tid; r < r1; r += kGbThreads) {
-      uint64_t v[W];
-      if constexpr (W == 2) {
-        const ulonglong2 t = __ldcs(reinterpret_cast<const ulonglong2 *>(a.rec) + r);
-        v[0] = t.x;
-        v[1] = t.y;
-      } else if constexpr (W == 4) {
-        const ulonglong2 t0 = __ldcs(reinterpret_cast<const ulonglong2 *>(a.rec + r * 4));
-        const ulonglong2 t1 = __ldcs(reinterpret_cast<const ulonglong2 *>(a.rec + r * 4 + 2));
-        v[0] = t0.x; v[1] = t0.y; v[2] = t1.x; v[3] = t1.y;
-      } else {
+    // ---- pass 1: every distinct key gets a slot and a group id
+    uint64_t kept[kGbKeep][W];
+    int kept_slot[kGbKeep];
 #pragma unroll
-        for (int w = 0; w < W; w++) v[w] = ld_stream_u64(a.rec + r * W + w);
+    for (int k = 0; k < kGbKeep; k++) {
+      const int64_t r = r0 + tid + (int64_t)k * kGbThreads;
+      kept_slot[k] = -2;
+      if (r < r1) {
+        load_row(r, kept[k]);
+        kept_slot[k] = find_slot(kept[k][0], true);
       }
-      const unsigned long long key = v[0];
-      // find or claim the key's slot
-      int slot = -1;
-      if (key == kGbEmpty) {
-        slot = kGbSlots;
-        s_special = 1;  // benign race: every writer stores 1
-      } else {
-        unsigned int h = (unsigned int)((key * 0x9E3779B97F4A7C15ULL) >> 40) & (kGbSlots - 1);
-        for (int probes = 0; probes < kGbSlots; probes++) {
-          unsigned long long cur = keys[h];
-          if (cur == kGbEmpty) cur = atomicCAS(&keys[h], kGbEmpty, key);
-          if (cur == kGbEmpty || cur == key) {
-            slot = (int)h;
-            break;
-          }
-          h = (h + 1) & (kGbSlots - 1);
-        }
-      }
-      if (slot < 0) {
-        *a.overflow = 1;
-        continue;
-      }
+    }
+    for (int64_t r = r0 + tid + (int64_t)kGbKeep * kGbThreads; r < r1; r += kGbThreads) {  // long bins only (one hot key)
+      uint64_t v[W];
+      load_row(r, v);
+      if (find_slot(v[0], true) < 0) *a.overflow = 1;
+    }
+    __syncthreads();
+    unsigned int ng = s_ng;
+    if (ng > (unsigned int)kGbSlots) {  // cannot happen while a bin has fewer rows than the table has slots; never index past the states
+      if (tid == 0) *a.overflow = 1;
+      ng = kGbSlots;
+    }
+    unsigned int R = ng ? kGbSlots / ng : 1;
+    if (R > kGbThreads / 32) R = kGbThreads / 32;
+    if (R < 1) R = 1;
+    const unsigned int rep_base = (warp % R) * ng;
+    if (tid == 0 && ng) base_reg = atomicAdd(a.out_cursor, (unsigned long long)ng);  // consumed after pass 2
+
+    // ---- pass 2: fold every row into its group's state (replica of this warp)
+    // The lanes of a warp that hold the same group (match.any) first combine their contributions in a tree over their
+    // ranks -- log2(multiplicity) rounds of one shuffle per aggregate -- and only the lowest lane of each group touches
+    // the state word: with PLAIN loads and stores when the warp owns its replica (R == warps per CTA), else with one
+    // atomic per group instead of one per row. Letting every row update the state cost 12 cycles per row in
+    // compare-and-swap traffic (5.3 ms for 125M rows with ~15 groups per bin), taking turns lane by lane 45 warp
+    // instructions per row (ncu, profiles/r02_groupby_notes.md).
+    const bool private_replica = R == kGbThreads / 32;
+    const unsigned int lane = tid & 31, lt = (1u << lane) - 1;
+    auto fold = [&](const uint64_t (&v)[W], int slot) {  // warp-uniform call; slot < 0: this lane has no row
+      const bool valid = slot >= 0;
+      const unsigned int e = rep_base + (valid ? gid_of[slot] : 0u);
+      const unsigned int peers = __match_any_sync(0xffffffffu, valid ? e : (0xFFFF0000u | lane));
+      const unsigned int rank = __popc(peers & lt), m = __popc(peers);
+      const unsigned int maxm = __reduce_max_sync(0xffffffffu, valid ? m : 1u);
+      unsigned long long c[kGbMaxAggs];
 #pragma unroll
       for (int ag = 0; ag < kGbMaxAggs; ag++) {
-        if (ag >= a.naggs) break;
-        unsigned long long *st = &state[ag * STRIDE + slot];
-        const int op = a.op[ag];
-        if (op == GB_COUNT) {
-          atomicAdd(st, 1ull);
-        } else if (op == GB_SUM_INT) {
-          atomicAdd(st, (unsigned long long)gb_pick<W>(v, a.src[ag]));
-        } else if (op == GB_SUM_F64) {
-          const double x = __longlong_as_double((long long)gb_pick<W>(v, a.src[ag]));
-          unsigned long long seen = *st, prev;
-          do {
-            prev = seen;
-            seen = atomicCAS(st, prev, (unsigned long long)__double_as_longlong(__longlong_as_double((long long)prev) + x));
-          } while (seen != prev);
+        c[ag] = 0;
+        if (ag < a.naggs) {
+          const uint64_t bits = gb_pick<W>(v, a.src[ag]);
+          c[ag] = a.op[ag] == GB_COUNT ? 1ull : ((a.op[ag] == GB_MIN || a.op[ag] == GB_MAX) ? gb_encode(bits, a.enc[ag]) : bits);
+        }
+      }
+      for (unsigned int step = 1; step < maxm; step <<= 1) {
+        const bool taker = valid && (rank & (2 * step - 1)) == 0 && rank + step < m;
+        const int from = taker ? (int)__fns(peers, 0, (int)(rank + step + 1)) : (int)lane;
+#pragma unroll
+        for (int ag = 0; ag < kGbMaxAggs; ag++) {
+          if (ag >= a.naggs) break;
+          const unsigned long long other = __shfl_sync(0xffffffffu, c[ag], from);
+          if (taker) c[ag] = gb_merge(c[ag], other, a.op[ag]);
+        }
+      }
+      if (valid && rank == 0) {
+        if (private_replica || a.naggs == 1) {
+#pragma unroll
+          for (int ag = 0; ag < kGbMaxAggs; ag++) {
+            if (ag >= a.naggs) break;
+            unsigned long long *st = &state[ag * kGbSlots + e];
+            if (private_replica) *st = gb_merge(*st, c[ag], a.op[ag]);
+            else gb_update_enc(st, a.op[ag], c[ag]);
+          }
         } else {
-          const unsigned long long e = gb_encode(gb_pick<W>(v, a.src[ag]), a.enc[ag]);
-          unsigned long long seen = *st;
-          while (op == GB_MIN ? e < seen : e > seen) {  // only a better value ever reaches the atomic
-            const unsigned long long prev = atomicCAS(st, seen, e);
-            if (prev == seen) break;
-            seen = prev;
+          // Several aggregates on a replica that other warps share: ONE returning atomic (the entry's lock) and plain
+          // read-modify-writes under it, instead of one atomic or compare-and-swap loop per aggregate -- returning
+          // shared-memory atomics cost the SM ~2 cycles per lane each, which at four per row was the kernel's bound
+          // (3.8 ms for 125M rows). Lanes of one warp never want the same lock here (one leader per group), and
+          // independent thread scheduling lets a waiting lane spin while the holder finishes.
+          bool done = false;
+          while (!done) {
+            if (atomicExch(&locks[e], 1u) == 0u) {
+#pragma unroll
+              for (int ag = 0; ag < kGbMaxAggs; ag++) {
+                if (ag >= a.naggs) break;
+                volatile unsigned long long *st = &state[ag * kGbSlots + e];
+                *st = gb_merge(*st, c[ag], a.op[ag]);
+              }
+              __threadfence_block();
+              *reinterpret_cast<volatile unsigned int *>(&locks[e]) = 0u;
+              done = true;
+            }
           }
         }
       }
+    };
+#pragma unroll
+    for (int k = 0; k < kGbKeep; k++) {
+      if (kept_slot[k] == -1) *a.overflow = 1;
+      if (__any_sync(0xffffffffu, kept_slot[k] >= 0)) fold(kept[k], kept_slot[k]);
+    }
+    for (int64_t rb = r0 + (int64_t)kGbKeep * kGbThreads + (tid & ~31); rb < r1; rb += kGbThreads) {  // warp-uniform trip count
+      const int64_t r = rb + lane;
+      uint64_t v[W];
+      int slot = -1;
+      if (r < r1) {
+        load_row(r, v);
+        slot = find_slot(v[0], false);
+      } else {
+#pragma unroll
+        for (int w = 0; w < W; w++) v[w] = 0;
+      }
+      fold(v, slot);
     }
     __syncthreads();
-    // emit: compact the occupied slots, reserve the bin's output range once, write the columns, reset the slots
-    for (int i = tid; i < kGbSlots; i += kGbThreads)
-      if (keys[i] != kGbEmpty) list[atomicAdd(&s_ngroups, 1u)] = (unsigned short)i;
+
+    // ---- emit: merge the replicas, write the columns, clean the table (the bin's output range was reserved after pass 1)
+    if (tid == 0) s_base = base_reg;
     __syncthreads();
-    if (tid == 0) {
-      if (s_special) list[s_ngroups++] = (unsigned short)kGbSlots;
-      s_base = atomicAdd(a.out_cursor, (unsigned long long)s_ngroups);
-    }
-    __syncthreads();
-    const unsigned int ng = s_ngroups;
     const bool fits = (int64_t)(s_base + ng) <= a.capacity;
-    for (unsigned int j = tid; j < ng; j += kGbThreads) {
-      const int slot = list[j];
-      const int64_t o = (int64_t)s_base + j;
+    for (unsigned int g = tid; g < ng; g += kGbThreads) {
+      const int slot = slot_of[g];
+      const int64_t o = (int64_t)s_base + g;
       if (fits) a.out_key[o] = slot == kGbSlots ? kGbEmpty : keys[slot];
       keys[slot] = kGbEmpty;
 #pragma unroll
       for (int ag = 0; ag < kGbMaxAggs; ag++) {
         if (ag >= a.naggs) break;
-        const unsigned long long w = state[ag * STRIDE + slot];
-        if (fits) a.out_agg[ag][o] = (a.op[ag] == GB_MIN || a.op[ag] == GB_MAX) ? gb_decode(w, a.enc[ag]) : w;
-        state[ag * STRIDE + slot] = a.init[ag];
+        unsigned long long acc = state[ag * kGbSlots + g];
+        for (unsigned int rp = 1; rp < R; rp++) acc = gb_merge(acc, state[ag * kGbSlots + rp * ng + g], a.op[ag]);
+        if (fits) a.out_agg[ag][o] = (a.op[ag] == GB_MIN || a.op[ag] == GB_MAX) ? gb_decode(acc, a.enc[ag]) : acc;
       }
     }
     __syncthreads();
+    for (int ag = 0; ag < a.naggs; ag++)
+      for (unsigned int i = tid; i < R * ng; i += kGbThreads) state[ag * kGbSlots + i] = a.init[ag];
     if (tid == 0) {
-      s_ngroups = 0;
+      s_ng = 0;
       s_special = 0;
+      s_bin = next_bin;
     }
   }
 }
 
-static size_t gb_smem_bytes(int naggs) {
-  return (size_t)(kGbSlots + 2) * 8 * (1 + naggs) + (size_t)(kGbSlots + 2) * 2 + 16;
+static size_t gb_smem_bytes(int naggs, int slots) {
+  return (size_t)(slots + 2) * 8 + (size_t)slots * 8 * naggs + (size_t)(slots + 2) * 2 * 2 + (size_t)slots * 4 + 16;
+}
+
+template <int W, int THREADS>
+static int launch_groupby_cfg(const GbArgs &a, int grid, cudaStream_t s) {
+  static PerDeviceOnce attr_once;
+  if (attr_once.first()) CYL_CUDA(cudaFuncSetAttribute(groupby_fused8_kernel<W, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+  groupby_fused8_kernel<W, THREADS><<<grid, THREADS, gb_smem_bytes(a.naggs, a.slots), s>>>(a);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
 }
 
 template <int W>
 static int launch_groupby(const GbArgs &a, int grid, cudaStream_t s) {
-  static PerDeviceOnce attr_once;
-  if (attr_once.first()) CYL_CUDA(cudaFuncSetAttribute(groupby_fused8_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gb_smem_bytes(kGbMaxAggs)));
-  groupby_fused8_kernel<W><<<grid, kGbThreads, gb_smem_bytes(a.naggs), s>>>(a);
-  CYL_LAUNCH_CHECK();
-  return CYL_OK;
+  switch (g_gb_threads) {
+    case 1024: return launch_groupby_cfg<W, 1024>(a, grid, s);
+    case 512: return launch_groupby_cfg<W, 512>(a, grid, s);
+    default: return launch_groupby_cfg<W, 256>(a, grid, s);
+  }
 }
 
 static bool gb_key_type_ok(int32_t t) {
@@ -255,9 +407,10 @@ int cyl_groupby_fused(const cyl_column_t *key, const cyl_column_t *values, int32
   cols[0] = *key;
   for (int v = 0; v < nvalues; v++) cols[1 + v] = values[v];
 
-  // bins of ~2000 rows on average: at most that many groups per bin, half the table's slots
+  // bins of <= kGbBinRows rows on average: at most that many groups per bin, half the table's slots
   int64_t nbins = 1;
-  while (nbins * 2000 < n && nbins < (1ll << 22)) nbins *= 2;
+  while (nbins * (int64_t)(g_gb_slots * 47 / 100) < n && nbins < (1ll << 22)) nbins *= 2;
+  if (g_gb_bins_log2 > 0) nbins = 1ll << g_gb_bins_log2;
   int bits = 0;
   while ((1ll << bits) < nbins) bits++;
   const int shift = 64 - bits;
@@ -311,12 +464,16 @@ int cyl_groupby_fused(const cyl_column_t *key, const cyl_column_t *values, int32
   }
   a.out_key = static_cast<uint64_t *>(out_key);
   a.capacity = capacity;
+  a.slots = g_gb_slots;
   CYL_TRY(counters.alloc(64, s));
   CYL_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
   a.out_cursor = counters.as<unsigned long long>();
   a.work_counter = reinterpret_cast<unsigned int *>(counters.as<char>() + 16);
   a.overflow = reinterpret_cast<int *>(counters.as<char>() + 32);
-  int64_t grid = num_sms();
+  int64_t per_sm = (200 * 1024) / (int64_t)(gb_smem_bytes(naggs, g_gb_slots) + 1024);
+  if (per_sm > 1024 / g_gb_threads) per_sm = 1024 / g_gb_threads;
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)num_sms() * per_sm;
   if (grid > nbins) grid = nbins;
   {
     ProfScope ps("groupby_fused_aggregate", s);

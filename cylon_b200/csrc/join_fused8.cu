@@ -444,10 +444,8 @@ static int f8_partition_blocks(const cyl_column_t *cols, int ncols, int key, int
 // shared-memory atomicAdd below (passes 0.70 -> 1.01-1.13 ms), linking the join's chains in rounds of plain stores
 // instead of atomicExch (probe 2.49 -> 2.75 ms), and join CTAs of 128 / 256 threads over 2^17 / 2^16 smaller bins (probe
 // 2.19 / 2.30 ms but histogram 0.66 / 0.42 ms: no gain for the step).
-void fused8_tune(int key, int value) {
-  (void)key;
-  (void)value;
-}
+void groupby_fused8_tune(int key, int value);
+void fused8_tune(int key, int value) { groupby_fused8_tune(key, value); }
 constexpr int kRsThreads = 512;  // == kRsMaxDigits: one digit per thread in the per-tile scan
 static int g_force_bins_log2 = 0;
 void fused8_force_bins_log2(int bits) { g_force_bins_log2 = bits; }

@@ -200,6 +200,72 @@ Status Split(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *ta
   return Status::OK();
 }
 
+// ---- the reference's host-vector signatures (partition/partition.hpp:32-42,76-90; partition.cpp:66-217) over the device forms
+Status MapToHashPartitions(const std::shared_ptr<Table> &table, const std::vector<int32_t> &hash_column_idx, uint32_t num_partitions,
+                           std::vector<uint32_t> &target_partitions, std::vector<uint32_t> &partition_histogram) {
+  if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  uint32_t *pid = nullptr;
+  uint64_t *hist = nullptr;
+  RETURN_CYLON_STATUS_IF_FAILED(MapToHashPartitions(table, hash_column_idx, num_partitions, &pid, &hist));
+  cudaStream_t s = static_cast<cudaStream_t>(table->GetContext()->GetStream());
+  const int64_t n = table->Rows();
+  target_partitions.assign((size_t)n, 0);
+  std::vector<uint64_t> h64(num_partitions, 0);
+  cudaError_t e = cudaSuccess;
+  if (n > 0) e = cudaMemcpyAsync(target_partitions.data(), pid, (size_t)n * 4, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(h64.data(), hist, (size_t)num_partitions * 8, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  cyl_free(pid);
+  cyl_free(hist);
+  if (e != cudaSuccess) return Status(Code::ExecutionError, std::string("MapToHashPartitions: ") + cudaGetErrorString(e));
+  partition_histogram.assign(num_partitions, 0);
+  for (uint32_t p = 0; p < num_partitions; p++) partition_histogram[p] = (uint32_t)h64[p];  // the reference's counters are 32-bit
+  return Status::OK();
+}
+
+Status MapToHashPartitions(const std::shared_ptr<Table> &table, int32_t hash_column_idx, uint32_t num_partitions,
+                           std::vector<uint32_t> &target_partitions, std::vector<uint32_t> &partition_histogram) {
+  return MapToHashPartitions(table, std::vector<int32_t>{hash_column_idx}, num_partitions, target_partitions, partition_histogram);
+}
+
+Status Split(const std::shared_ptr<Table> &table, uint32_t num_partitions, const std::vector<uint32_t> &target_partitions,
+             std::vector<std::shared_ptr<Table>> &output) {
+  if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  if ((int64_t)target_partitions.size() != table->Rows()) return Status(Code::Invalid, "Split: target_partitions has a different length than the table");
+  for (uint32_t p : target_partitions)
+    if (p >= num_partitions) return Status(Code::IndexError, "Split: target partition out of range");
+  void *stream = table->GetContext()->GetStream();
+  DevBuf pid;
+  RETURN_CYLON_STATUS_IF_FAILED(pid.alloc((target_partitions.size() + 1) * 4, stream));
+  if (!target_partitions.empty())
+    CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(pid.p, target_partitions.data(), target_partitions.size() * 4, cudaMemcpyHostToDevice,
+                                          static_cast<cudaStream_t>(stream)));
+  Status st = Split(table, num_partitions, pid.as<uint32_t>(), output);
+  CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));  // the host vector may go away now
+  return st;
+}
+
+Status Split(const std::shared_ptr<Table> &table, uint32_t num_partitions, const std::vector<uint32_t> &target_partitions,
+             const std::vector<uint32_t> &partition_hist_ptr, std::vector<std::shared_ptr<Table>> &output) {
+  if (partition_hist_ptr.size() != num_partitions) return Status(Code::Invalid, "Split: partition histogram length != num_partitions");
+  RETURN_CYLON_STATUS_IF_FAILED(Split(table, num_partitions, target_partitions, output));
+  for (uint32_t p = 0; p < num_partitions; p++)
+    if (output[p]->Rows() != (int64_t)partition_hist_ptr[p]) return Status(Code::Invalid, "Split: partition histogram does not match target_partitions");
+  return Status::OK();
+}
+
+Status PartitionByHashing(const std::shared_ptr<Table> &table, const std::vector<int32_t> &hash_cols, uint32_t num_partitions,
+                          std::vector<std::shared_ptr<Table>> &partitions) {  // partition.cpp:200-217: MapToHashPartitions + Split
+  if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");
+  if (num_partitions < 1) return Status(Code::Invalid, "num_partitions must be positive");
+  std::shared_ptr<Table> t = table;
+  std::unordered_map<int, std::shared_ptr<Table>> parts;
+  RETURN_CYLON_STATUS_IF_FAILED(HashPartition(t, std::vector<int>(hash_cols.begin(), hash_cols.end()), (int)num_partitions, &parts));
+  partitions.clear();
+  for (uint32_t p = 0; p < num_partitions; p++) partitions.push_back(parts[(int)p]);
+  return Status::OK();
+}
+
 Status HashPartition(std::shared_ptr<Table> &table, const std::vector<int> &hash_columns, int no_of_partitions,
                      std::unordered_map<int, std::shared_ptr<Table>> *out) {  // table.cpp:384-426
   if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");

@@ -14,6 +14,10 @@
 #include "join/join_config.hpp"
 #include "status.hpp"
 
+namespace arrow {
+class Table;
+}
+
 namespace cylon {
 
 class Table {
@@ -25,6 +29,12 @@ class Table {
   // ... or from host Arrow-layout buffers (copied to HBM on the context's stream)
   static Status FromHostColumns(std::shared_ptr<CylonContext> &ctx, const std::vector<cyl_column_t> &host_columns,
                                 const std::vector<std::string> &names, std::shared_ptr<Table> &out);
+
+  // Arrow host tables in and out (table.hpp:76,96,146 of the reference). Declared here, defined inline in
+  // <cylon/arrow_bridge.hpp>, which needs the Arrow C++ headers: include it where these are called.
+  static Status FromArrowTable(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<arrow::Table> &table, std::shared_ptr<Table> &out);
+  Status ToArrowTable(std::shared_ptr<arrow::Table> &output);
+  std::shared_ptr<arrow::Table> get_table();
 
   int64_t Rows() const { return columns_.empty() ? 0 : columns_[0]->length(); }  // table.hpp:146
   int32_t Columns() const { return (int32_t)columns_.size(); }                   // table.hpp:140

@@ -1,0 +1,115 @@
+// Reference-style user code over Arrow host tables: Table::FromArrowTable -> operators -> ToArrowTable / get_table, and the
+// std::vector forms of MapToHashPartitions / Split / PartitionByHashing (partition/partition.hpp:32-90), written the way
+// cpp/test/partition_test.cpp:32-79 and cpp/src/examples/join_example.cpp use them. Without arguments it only has to
+// build and link; "run" executes on cuda:0 and checks the identities the reference's partition test checks.
+#include <arrow/api.h>
+
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <vector>
+
+#include <cylon/arrow_bridge.hpp>
+#include <cylon/ctx/cylon_context.hpp>
+#include <cylon/join/join_config.hpp>
+#include <cylon/partition/partition.hpp>
+#include <cylon/table.hpp>
+
+#define CHECK(cond)                                                      \
+  do {                                                                   \
+    if (!(cond)) {                                                       \
+      std::fprintf(stderr, "FAILED %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+      return 1;                                                          \
+    }                                                                    \
+  } while (0)
+
+static std::shared_ptr<arrow::Table> MakeTable(int64_t n, int64_t dom, int seed, bool with_nulls) {
+  arrow::Int64Builder kb;
+  arrow::DoubleBuilder vb;
+  arrow::StringBuilder sb;
+  uint64_t x = 88172645463325252ull + (uint64_t)seed;
+  for (int64_t i = 0; i < n; i++) {
+    x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+    const int64_t k = (int64_t)(x % (uint64_t)dom);
+    (void)kb.Append(k);
+    if (with_nulls && i % 5 == 0) (void)vb.AppendNull(); else (void)vb.Append((double)k * 0.5);
+    (void)sb.Append("s" + std::to_string(k % 7));
+  }
+  std::shared_ptr<arrow::Array> k, v, s;
+  (void)kb.Finish(&k); (void)vb.Finish(&v); (void)sb.Finish(&s);
+  return arrow::Table::Make(arrow::schema({arrow::field("k", arrow::int64()), arrow::field("v", arrow::float64()), arrow::field("s", arrow::utf8())}),
+                            {k, v, s});
+}
+
+static int run() {
+  auto ctx = cylon::CylonContext::Init();
+  CHECK(ctx != nullptr);
+  const int64_t n = 5000;
+  auto at = MakeTable(n, 400, 1, true);
+  auto sliced = at->Slice(3, n - 10);  // non-zero array offsets: the validity bitmap has to be re-aligned
+  std::shared_ptr<cylon::Table> t, ts;
+  CHECK(cylon::Table::FromArrowTable(ctx, at, t).is_ok());
+  CHECK(cylon::Table::FromArrowTable(ctx, sliced, ts).is_ok());
+  CHECK(t->Rows() == n && t->Columns() == 3 && ts->Rows() == n - 10);
+
+  // round trip: same values, same nulls, same names
+  std::shared_ptr<arrow::Table> back;
+  CHECK(ts->ToArrowTable(back).is_ok());
+  CHECK(back->Equals(*sliced->CombineChunks().ValueOrDie()));
+  CHECK(t->get_table() != nullptr && t->get_table()->Equals(*at));
+
+  // partition_test.cpp:32-79: pid == key % W, histogram sums to the row count, Split sizes == histogram
+  const uint32_t W = 6;
+  std::vector<uint32_t> pid, hist;
+  CHECK(cylon::MapToHashPartitions(t, 0, W, pid, hist).is_ok());
+  CHECK((int64_t)pid.size() == n && hist.size() == W);
+  auto keys = std::static_pointer_cast<arrow::Int64Array>(at->column(0)->chunk(0));
+  uint64_t total = 0;
+  for (uint32_t h : hist) total += h;
+  CHECK((int64_t)total == n);
+  for (int64_t i = 0; i < n; i++) CHECK(pid[i] == (uint32_t)keys->Value(i) % W);
+  std::vector<std::shared_ptr<cylon::Table>> parts, parts5, hashed;
+  CHECK(cylon::Split(t, W, pid, parts).is_ok());
+  CHECK(cylon::Split(t, W, pid, hist, parts5).is_ok());
+  CHECK(cylon::PartitionByHashing(t, {0}, W, hashed).is_ok());
+  CHECK(parts.size() == W && parts5.size() == W && hashed.size() == W);
+  for (uint32_t p = 0; p < W; p++) {
+    CHECK(parts[p]->Rows() == (int64_t)hist[p] && hashed[p]->Rows() == (int64_t)hist[p]);
+    auto ap = parts[p]->get_table();
+    CHECK(ap != nullptr && ap->Equals(*hashed[p]->get_table()));  // same stable order either way
+    auto pk = std::static_pointer_cast<arrow::Int64Array>(ap->column(0)->chunk(0));
+    for (int64_t i = 0; i < pk->length(); i++) CHECK((uint32_t)pk->Value(i) % W == p);
+  }
+  std::vector<uint32_t> bad_hist(hist);
+  bad_hist[0] += 1;
+  CHECK(!cylon::Split(t, W, pid, bad_hist, parts5).is_ok());
+
+  // a join over Arrow tables end to end: every output row pairs equal keys, and the count is sum cntL * cntR
+  auto ar = MakeTable(3000, 400, 2, false);
+  std::shared_ptr<cylon::Table> r, joined;
+  CHECK(cylon::Table::FromArrowTable(ctx, ar, r).is_ok());
+  auto cfg = cylon::join::config::JoinConfig::InnerJoin(0, 0, cylon::join::config::JoinAlgorithm::HASH, "l_", "r_");
+  CHECK(cylon::Join(t, r, cfg, joined).is_ok());
+  std::map<int64_t, int64_t> cl, cr;
+  auto rk = std::static_pointer_cast<arrow::Int64Array>(ar->column(0)->chunk(0));
+  for (int64_t i = 0; i < n; i++) cl[keys->Value(i)]++;
+  for (int64_t i = 0; i < rk->length(); i++) cr[rk->Value(i)]++;
+  int64_t expect = 0;
+  for (auto &kv : cl) expect += kv.second * cr[kv.first];
+  auto aj = joined->get_table();
+  CHECK(aj != nullptr && aj->num_rows() == expect && aj->num_columns() == 6);
+  CHECK(aj->field(0)->name() == "l_k" && aj->field(3)->name() == "r_k");
+  auto jl = std::static_pointer_cast<arrow::Int64Array>(aj->column(0)->chunk(0));
+  auto jr = std::static_pointer_cast<arrow::Int64Array>(aj->column(3)->chunk(0));
+  for (int64_t i = 0; i < aj->num_rows(); i++) CHECK(jl->Value(i) == jr->Value(i));
+  CHECK(aj->column(1)->null_count() == 0);  // the join drops source nulls (copy_arrray.cpp:47)
+  ctx->Finalize();
+  std::printf("ARROW_BRIDGE_OK rows=%lld\n", (long long)aj->num_rows());
+  return 0;
+}
+
+int main(int argc, char **argv) {
+  if (argc > 1 && std::strcmp(argv[1], "run") == 0) return run();
+  return 0;  // building and linking is the test
+}
