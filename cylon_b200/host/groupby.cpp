@@ -45,6 +45,7 @@ Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_
     }
     if (n > 0 && cyl_groupby_fused_supported(&key, values.data(), (int32_t)values.size(), agg_value.data(), agg_op.data(), (int32_t)agg_op.size())) {
       int64_t capacity = std::min<int64_t>(n, n / 4 + (1 << 20));
+      bool fused_failed = false;
       for (int attempt = 0; attempt < 2; attempt++) {
         std::vector<std::shared_ptr<Column>> cols;
         std::shared_ptr<Column> kc;
@@ -62,8 +63,13 @@ Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_
           cols.push_back(col);
         }
         int64_t groups = 0;
-        CYL_RETURN_IF_FAILED(cyl_groupby_fused(&key, values.data(), (int32_t)values.size(), agg_value.data(), agg_op.data(), (int32_t)agg_op.size(),
-                                               capacity, kc->mutable_data(), outs.data(), &groups, stream));
+        const int rc = cyl_groupby_fused(&key, values.data(), (int32_t)values.size(), agg_value.data(), agg_op.data(), (int32_t)agg_op.size(),
+                                         capacity, kc->mutable_data(), outs.data(), &groups, stream);
+        if (rc == CYL_CapacityError) {  // keys that pile into one bin of the shared-memory table: the general path has no such limit
+          fused_failed = true;
+          break;
+        }
+        if (rc != CYL_OK) return detail::FromCode(rc);
         if (groups <= capacity) {
           for (auto &c : cols) c->truncate(groups);
           output = std::make_shared<Table>(std::move(cols), ctx);
@@ -71,7 +77,7 @@ Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_
         }
         capacity = groups;  // the optimistic capacity was too small: the exact count is known now
       }
-      return Status(Code::ExecutionError, "fused group-by did not fit its exact capacity");
+      if (!fused_failed) return Status(Code::ExecutionError, "fused group-by did not fit its exact capacity");
     }
   }
 
