@@ -162,8 +162,10 @@ Status Join(std::shared_ptr<Table> &left, std::shared_ptr<Table> &right, const j
   const auto lk = detail::Descs(*left, lidx), rk = detail::Descs(*right, ridx);
   const int jt = (int)cfg.GetType();
 
-  // fast path: radix-partitioned shared-memory join that writes the result columns directly
-  if (cfg.GetAlgorithm() == join::config::HASH && lidx.size() == 1 && ctx->GetConfig("cylon.join.fused", "1") != "0") {
+  // fast path: radix-partitioned shared-memory join that writes the result columns directly. JoinAlgorithm does not
+  // matter here: HASH and SORT are two CPU strategies for the same row multiset (join/join.cpp:80-100); the LSD radix
+  // sort + merge of join_sort.cu remains the general SORT path ("cylon.join.fused" = "0", strings, wide tables).
+  if (lidx.size() == 1 && ctx->GetConfig("cylon.join.fused", "1") != "0") {
     const auto lall = detail::AllDescs(*left), rall = detail::AllDescs(*right);
     if (cyl_hash_join_fused_supported(lall.data(), (int32_t)lall.size(), lidx[0], rall.data(), (int32_t)rall.size(), ridx[0], jt)) {
       const int64_t nl = left->Rows(), nr = right->Rows();
@@ -191,6 +193,55 @@ Status Join(std::shared_ptr<Table> &left, std::shared_ptr<Table> &right, const j
           return Status::OK();
         }
         capacity = m;  // the optimistic capacity was too small: the exact size is known now
+      }
+      return Status(Code::ExecutionError, "fused join did not fit its exact capacity");
+    }
+  }
+
+  // second fast path (join_fused8x.cu): outer joins, two-column keys, 4/8-byte columns -- for HASH and SORT alike, since
+  // both algorithms of the reference produce the same row multiset (join/join.cpp:80-100)
+  if ((lidx.size() == 1 || lidx.size() == 2) && ctx->GetConfig("cylon.join.fused", "1") != "0") {
+    const auto lall = detail::AllDescs(*left), rall = detail::AllDescs(*right);
+    std::vector<int32_t> lk32(lidx.begin(), lidx.end()), rk32(ridx.begin(), ridx.end());
+    if (cyl_join_fused_supported(lall.data(), (int32_t)lall.size(), lk32.data(), rall.data(), (int32_t)rall.size(), rk32.data(), (int32_t)lk32.size(), jt)) {
+      const int64_t nl = left->Rows(), nr = right->Rows();
+      const bool left_null = jt == CYL_JOIN_RIGHT || jt == CYL_JOIN_FULL_OUTER;
+      const bool right_null = jt == CYL_JOIN_LEFT || jt == CYL_JOIN_FULL_OUTER;
+      int64_t capacity = std::max(nl, nr) + std::max(nl, nr) / 8 + 1024;
+      if (jt == CYL_JOIN_FULL_OUTER) capacity = nl + nr + 1024;
+      for (int attempt = 0; attempt < 2; attempt++) {
+        std::vector<std::shared_ptr<Column>> cols;
+        std::vector<void *> outs;
+        for (int side = 0; side < 2; side++) {
+          const Table &t = side == 0 ? *left : *right;
+          const std::string &prefix = side == 0 ? cfg.GetLeftTableSuffix() : cfg.GetRightTableSuffix();
+          const bool nullable = side == 0 ? left_null : right_null;
+          for (const auto &src : t.GetColumns()) {
+            std::shared_ptr<Column> col;
+            RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(prefix + src->name(), src->type(), src->byte_width(), capacity,
+                                                           capacity * (int64_t)src->byte_width(), nullable, stream, &col));
+            outs.push_back(col->mutable_data());
+            cols.push_back(col);
+          }
+        }
+        detail::DevBuf lvalid, rvalid;
+        if (left_null) RETURN_CYLON_STATUS_IF_FAILED(lvalid.alloc((size_t)capacity + 16, stream));
+        if (right_null) RETURN_CYLON_STATUS_IF_FAILED(rvalid.alloc((size_t)capacity + 16, stream));
+        int64_t m = 0;
+        CYL_RETURN_IF_FAILED(cyl_join_fused(lall.data(), (int32_t)lall.size(), lk32.data(), rall.data(), (int32_t)rall.size(), rk32.data(),
+                                            (int32_t)lk32.size(), jt, capacity, outs.data(), left_null ? lvalid.as<uint8_t>() : nullptr,
+                                            right_null ? rvalid.as<uint8_t>() : nullptr, &m, stream));
+        if (m <= capacity) {
+          for (size_t c = 0; c < cols.size(); c++) {
+            cols[c]->truncate(m);
+            const bool is_left = c < lall.size();
+            if ((is_left && left_null) || (!is_left && right_null))
+              CYL_RETURN_IF_FAILED(cyl_pack_validity(is_left ? lvalid.as<uint8_t>() : rvalid.as<uint8_t>(), m, cols[c]->mutable_validity(), stream));
+          }
+          out = std::make_shared<Table>(std::move(cols), ctx);
+          return Status::OK();
+        }
+        capacity = m;
       }
       return Status(Code::ExecutionError, "fused join did not fit its exact capacity");
     }

@@ -172,6 +172,20 @@ int cyl_hash_join_fused_supported(const cyl_column_t *lcols /* host array */, in
 int cyl_hash_join_fused_inner(const cyl_column_t *lcols /* host array */, int32_t nlcols, int32_t lkey, const cyl_column_t *rcols /* host array */,
                               int32_t nrcols, int32_t rkey, int64_t nl, int64_t nr, int64_t capacity, void *const *out_cols /* host array */,
                               int64_t *num_rows /* host out */, void *stream);
+/* The same engine for LEFT / RIGHT / FULL_OUTER joins, keys of one or two columns and tables that mix 4- and 8-byte
+ * numeric / temporal columns (at most 4 record words per side; a two-column key uses one of them). out_cols: nlcols +
+ * nrcols device buffers of `capacity` values of each column's width, left columns first. left_valid / right_valid: device
+ * byte arrays of `capacity` entries, 1 where that side of the output row is present and 0 where it is null (required
+ * for the side(s) the join type can leave without a partner, may be NULL otherwise); pack them with cyl_pack_validity.
+ * Null slots hold zeros. Source validity is ignored as in the reference's join. Same capacity protocol as above. Used for
+ * JoinAlgorithm HASH and SORT alike: both produce this row multiset (join/join.cpp:80-100).
+ * Replaces the probe functions and build-side choice of join/hash_join.cpp:21-90,207-232, multi_index_hash_join
+ * (:92-186), do_multi_index_sorted_join (join/sort_join.cpp:396-556) and build_final_table (join/join_utils.cpp:126-181). */
+int cyl_join_fused_supported(const cyl_column_t *lcols /* host array */, int32_t nlcols, const int32_t *lkeys, const cyl_column_t *rcols /* host array */,
+                             int32_t nrcols, const int32_t *rkeys, int32_t nkeys, int32_t join_type);
+int cyl_join_fused(const cyl_column_t *lcols /* host array */, int32_t nlcols, const int32_t *lkeys, const cyl_column_t *rcols /* host array */,
+                   int32_t nrcols, const int32_t *rkeys, int32_t nkeys, int32_t join_type, int64_t capacity, void *const *out_cols /* host array */,
+                   uint8_t *left_valid, uint8_t *right_valid, int64_t *num_rows /* host out */, void *stream);
 /* Tuning/test hook with no reference counterpart: force 2^bits radix bins (1..18) in the all-8-byte fused join instead of
  * the count chosen from the build size; 0 restores the automatic choice. More bins than needed is always valid (they
  * are just emptier), so tests use it to reach the many-bin code paths (512-way digits, split histogram) with small

@@ -94,7 +94,7 @@ def test_fused_supported_predicate(cy):
     s = [cy.DCol.from_numpy(np.arange(4, dtype=np.int64)), cy.DCol.from_numpy(["a", "b", "c", "d"])]
     f = cy.lib().cyl_hash_join_fused_supported
     assert f(cy.c_columns(a), 2, 0, cy.c_columns(a), 2, 0, orc.INNER) == 1
-    assert f(cy.c_columns(a), 2, 0, cy.c_columns(a), 2, 0, orc.LEFT) == 0      # outer joins take the general path
+    assert f(cy.c_columns(a), 2, 0, cy.c_columns(a), 2, 0, orc.LEFT) == 0      # outer joins: cyl_join_fused (join_fused8x.cu)
     assert f(cy.c_columns(a), 2, 0, cy.c_columns(s), 2, 0, orc.INNER) == 0     # strings take the general path
     assert f(cy.c_columns(a), 2, 0, cy.c_columns(a), 2, 1, orc.INNER) == 0     # key types differ
 
@@ -109,7 +109,9 @@ def test_table_join_takes_fused_path_and_matches_general_path():
     r = [orc.col(rk, name="k"), orc.col(rv, name="v")]
     L, R = from_orc(api, ctx, l), from_orc(api, ctx, r)
     fused = L.join(R, "inner", "hash", [0], [0], "l_", "r_")
+    ctx.add_config("cylon.join.fused", "0")  # the general path: LSD radix sort + merge, index vectors, gather
     general = L.join(R, "inner", "sort", [0], [0], "l_", "r_")
+    ctx.add_config("cylon.join.fused", "1")
     assert fused.row_count == general.row_count
     assert fused.checksum() == general.checksum()
     m_ref, cs_ref = orc.join_i64_f64(lk, lv, rk, rv, orc.INNER, orc.HASH)
@@ -138,7 +140,9 @@ def test_fused_join_large(skew):
     m_ref, cs_ref = orc.join_i64_f64(lk, lv, rk, rv, orc.INNER, orc.HASH)
     assert fused.row_count == m_ref
     assert fused.checksum() == cs_ref
+    ctx.add_config("cylon.join.fused", "0")
     general = L.join(R, "inner", "sort", [0], [0])
+    ctx.add_config("cylon.join.fused", "1")
     assert general.row_count == m_ref and general.checksum() == cs_ref
     ctx.finalize()
 
