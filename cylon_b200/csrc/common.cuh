@@ -55,6 +55,7 @@ struct ProfScope {
 cudaError_t pool_malloc(void **ptr, size_t bytes, cudaStream_t stream);
 cudaError_t pool_free(void *ptr, cudaStream_t stream);
 void pool_trim();  // cudaFree every parked block
+long long pool_generation();  // bumped by every pool_trim: cached mappings of this process's blocks are stale after a change
 
 // Stream-ordered scratch buffer from that allocator.
 struct Scratch {

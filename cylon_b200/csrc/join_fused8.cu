@@ -814,6 +814,10 @@ int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_
   // store per row (~37 G scattered stores/s chip-wide whatever the table size, so not TLB reach either), not the atomic.
   // So: block-private ranges only while a (tile, bin) run is long enough to fill lines, else shared cursors -- but
   // always the shared-memory histogram, which is 4x faster than global reductions.
+  if (n == 0) {  // nothing to move: every bin is empty
+    CYL_CUDA(cudaMemsetAsync(bin_off, 0, (size_t)(nbins + 1) * sizeof(int64_t), s));
+    return CYL_OK;
+  }
   const int64_t tile_guess = n / ((int64_t)num_sms() * 4) + 1;
   {  // large tables: two staged passes with coalesced stores instead of one pass of scattered stores
     const int kb = 64 - shift;

@@ -22,6 +22,7 @@
 //   * output rows carry one validity byte per row and nullable side, packed into Arrow validity bitmaps by the caller.
 #include "common.cuh"
 #include "join_fused.cuh"
+#include "scan.cuh"
 
 namespace cylb {
 
@@ -53,7 +54,34 @@ struct F8XArgs {
   unsigned long long *out_cursor;
   unsigned int *work_counter;
   uint8_t *pflag;                // [np] probe row matched in some build chunk (multi-chunk bins of outer joins)
+  const int64_t *slice_off;      // [nbins + 1] work items before each bin: a bin with many probe rows is cut into slices
+  uint8_t *bflag;                // [nb] FULL_OUTER, bins cut into slices: build row matched by some slice
+  unsigned int *bin_ticket;      // [nbins] FULL_OUTER: slices of the bin that have finished
 };
+
+// Probe rows one work item covers. A bin normally holds a few thousand probe rows (one item); a hot key on the probe side
+// puts millions into one bin (config 3: 12 % of the left table), which one CTA would chew through alone -- measured 27.7 ms
+// for 50M x 50M rows -- so such a bin becomes many items that each rebuild the bin's small table.
+constexpr int64_t kXSliceRows = 16 * kXThreads * kXProbeRows;
+
+// fullest bin of each side -> out[0] (left), out[1] (right)
+__global__ void x_maxbin_kernel(const int64_t *__restrict__ l_off, const int64_t *__restrict__ r_off, int64_t nbins, unsigned long long *__restrict__ out) {
+  unsigned long long ml = 0, mr = 0;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nbins; b += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned long long l = (unsigned long long)(l_off[b + 1] - l_off[b]), r = (unsigned long long)(r_off[b + 1] - r_off[b]);
+    ml = l > ml ? l : ml;
+    mr = r > mr ? r : mr;
+  }
+  if (ml) atomicMax(&out[0], ml);
+  if (mr) atomicMax(&out[1], mr);
+}
+
+__global__ void x_slices_kernel(const int64_t *__restrict__ p_off, int64_t nbins, uint32_t *__restrict__ nslices) {
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nbins; b += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t pn = p_off[b + 1] - p_off[b];
+    nslices[b] = pn <= kXSliceRows ? 1u : (uint32_t)((pn + kXSliceRows - 1) / kXSliceRows);
+  }
+}
 
 __device__ __forceinline__ uint32_t x_bucket(uint64_t k) { return (uint32_t)((k * 0x9E3779B97F4A7C15ULL) >> 38); }
 
@@ -97,7 +125,7 @@ __device__ __forceinline__ unsigned int x_block_scan(unsigned int c, unsigned in
 template <int BW, int PW>
 __global__ void __launch_bounds__(kXThreads, 2) fused8x_join_kernel(const __grid_constant__ F8XArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
-  __shared__ unsigned int s_bin;
+  __shared__ unsigned int s_bin, s_last;
   __shared__ unsigned int s_warp_tot[kXThreads / 32];
   __shared__ unsigned long long s_base;
   uint64_t *brec = reinterpret_cast<uint64_t *>(smem);                                  // [cap_rows][BW]
@@ -124,17 +152,33 @@ __global__ void __launch_bounds__(kXThreads, 2) fused8x_join_kernel(const __grid
     if (a.p.null_flag) a.p.null_flag[o] = has_p ? 1 : 0;
   };
 
+  const int64_t total_items = a.slice_off[a.nbins];
   while (true) {
     __syncthreads();
     if (tid == 0) s_bin = atomicAdd(a.work_counter, 1u);
     __syncthreads();
-    const int64_t bin = s_bin;
-    if (bin >= a.nbins) break;
+    const int64_t item = s_bin;
+    if (item >= total_items) break;
+    int64_t bin;
+    {  // last bin whose first item is <= item
+      int64_t lo = 0, hi = a.nbins;
+      while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (a.slice_off[mid] <= item) lo = mid; else hi = mid;
+      }
+      bin = lo;
+    }
+    const int64_t slice = item - a.slice_off[bin], nslices = a.slice_off[bin + 1] - a.slice_off[bin];
     const int64_t b0 = a.b_off[bin], b1 = a.b_off[bin + 1];
-    const int64_t p0 = a.p_off[bin], p1 = a.p_off[bin + 1];
+    int64_t p0 = a.p_off[bin], p1 = a.p_off[bin + 1];
     if (p1 == p0 && !(a.keep_build && b1 > b0)) continue;
     if (b1 == b0 && !(a.keep_probe && p1 > p0)) continue;
+    if (nslices > 1) {  // this item's share of the bin's probe rows
+      p0 += slice * kXSliceRows;
+      if (p1 > p0 + kXSliceRows) p1 = p0 + kXSliceRows;
+    }
     const bool multi_chunk = (b1 - b0) > a.cap_rows;
+    const bool shared_bin = nslices > 1;
 
     int64_t c0 = b0;
     do {  // build chunks: more than one only when a hot key overfills the bin; runs once with nb == 0 for an empty build side
@@ -213,7 +257,11 @@ __global__ void __launch_bounds__(kXThreads, 2) fused8x_join_kernel(const __grid
           }
         }
       }
-      if (a.keep_build && nb > 0) {  // FULL_OUTER: build rows of this chunk that no probe row matched
+      if (a.keep_build && nb > 0 && shared_bin) {  // other slices probe this chunk too: publish, the last slice settles it
+        __syncthreads();
+        for (int i = tid; i < nb; i += kXThreads)
+          if (bmatched[i]) a.bflag[c0 + i] = 1;
+      } else if (a.keep_build && nb > 0) {  // FULL_OUTER: build rows of this chunk that no probe row matched
         __syncthreads();
         unsigned int mine = 0;
         for (int i = tid; i < nb; i += kXThreads) mine += bmatched[i] ? 0u : 1u;
@@ -231,6 +279,25 @@ __global__ void __launch_bounds__(kXThreads, 2) fused8x_join_kernel(const __grid
       c0 += a.cap_rows;
     } while (c0 < b1);
 
+    if (a.keep_build && shared_bin) {  // FULL_OUTER, bin cut into slices: whoever finishes last emits the unmatched build rows
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) s_last = atomicAdd(&a.bin_ticket[bin], 1u) == (unsigned int)(nslices - 1) ? 1u : 0u;
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        const uint64_t none[PW] = {};
+        for (int64_t t0 = b0; t0 < b1; t0 += kXThreads) {
+          const int64_t i = t0 + tid;
+          const unsigned int mine = (i < b1 && !*reinterpret_cast<volatile uint8_t *>(&a.bflag[i])) ? 1u : 0u;
+          unsigned int total;
+          const unsigned int my_off = x_block_scan(mine, s_warp_tot, &total);
+          if (tid == 0 && total) s_base = atomicAdd(a.out_cursor, (unsigned long long)total);
+          __syncthreads();
+          if (mine && (int64_t)(s_base + total) <= a.capacity) emit((int64_t)s_base + my_off, a.brec + (size_t)i * BW, none, false);
+        }
+      }
+    }
     if (multi_chunk && a.keep_probe) {  // probe rows that matched in no chunk
       __threadfence();
       __syncthreads();
@@ -395,45 +462,73 @@ int cyl_join_fused(const cyl_column_t *lcols, int32_t nlcols, const int32_t *lke
   const bool left_can_be_null = join_type == CYL_JOIN_RIGHT || join_type == CYL_JOIN_FULL_OUTER;
   const bool right_can_be_null = join_type == CYL_JOIN_LEFT || join_type == CYL_JOIN_FULL_OUTER;
   if ((left_can_be_null && !left_valid) || (right_can_be_null && !right_valid)) return fail(CYL_Invalid, "cyl_join_fused: validity byte buffer missing");
-  // build side as the reference chooses it (hash_join.cpp:207-232): the preserved side of LEFT / RIGHT probes
-  bool build_right;
-  switch (join_type) {
-    case CYL_JOIN_LEFT: build_right = true; break;
-    case CYL_JOIN_RIGHT: build_right = false; break;
-    default: build_right = !(nl <= nr); break;
-  }
-  const cyl_column_t *bcols = build_right ? rcols : lcols, *pcols = build_right ? lcols : rcols;
-  const int nbc = build_right ? nrcols : nlcols, npc = build_right ? nlcols : nrcols;
-  const int32_t *bkeys = build_right ? rkeys : lkeys, *pkeys = build_right ? lkeys : rkeys;
-  const int64_t nb = build_right ? nr : nl, np = build_right ? nl : nr;
-
-  XWords bw, pw;
-  CYL_TRY(x_build_words(bcols, nbc, bkeys, nkeys, nb, &bw, s));
-  CYL_TRY(x_build_words(pcols, npc, pkeys, nkeys, np, &pw, s));
-
+  // Both tables are partitioned first; then the side whose fullest bin is smaller becomes the build side. The reference
+  // builds from the non-preserved side of a LEFT / RIGHT join and from the smaller table otherwise (hash_join.cpp:207-232),
+  // which only changes the order of its output. Here it decides the cost: a key with millions of rows on the BUILD side
+  // means thousands of build chunks and single probe rows that emit millions of matches from one thread (measured:
+  // FULL_OUTER of config 3 with the Zipf side as build took 2.8 s instead of 7 ms). Either side can be preserved in
+  // either role -- an unmatched preserved row is "probe row without partner" or "build row nobody matched".
+  XWords lw, rw;
+  CYL_TRY(x_build_words(lcols, nlcols, lkeys, nkeys, nl, &lw, s));
+  CYL_TRY(x_build_words(rcols, nrcols, rkeys, nkeys, nr, &rw, s));
   const size_t budget = 104 * 1024;
-  int cap = 16384 - 256, nheads = 0;
-  size_t smem_bytes = 0;
-  for (;; cap -= 256) {
-    nheads = 256;
-    while (nheads < cap * 2) nheads *= 2;
-    smem_bytes = (size_t)cap * bw.nwords * 8 + (size_t)nheads * 4 + (size_t)cap * 3 + 32;
-    if (smem_bytes <= budget || cap <= 256) break;
-  }
+  auto plan_cap = [&](int nwords, int *nheads_out, size_t *smem_out) {
+    int cap = 16384 - 256;
+    for (;; cap -= 256) {
+      int nheads = 256;
+      while (nheads < cap * 2) nheads *= 2;
+      const size_t bytes = (size_t)cap * nwords * 8 + (size_t)nheads * 4 + (size_t)cap * 3 + 32;
+      if (bytes <= budget || cap <= 256) {
+        *nheads_out = nheads;
+        *smem_out = bytes;
+        return cap;
+      }
+    }
+  };
+  int lheads = 0, rheads = 0;
+  size_t lsmem = 0, rsmem = 0;
+  const int lcap = plan_cap(lw.nwords, &lheads, &lsmem), rcap = plan_cap(rw.nwords, &rheads, &rsmem);
   int64_t nbins = 1;
-  while (nbins * (int64_t)(cap * 8 / 10) < nb && nbins < (1ll << 22)) nbins *= 2;
+  while ((nbins * (int64_t)(lcap * 8 / 10) < nl || nbins * (int64_t)(rcap * 8 / 10) < nr) && nbins < (1ll << 22)) nbins *= 2;
   int bits = 0;
   while ((1ll << bits) < nbins) bits++;
   const int shift = 64 - bits;
 
-  Scratch brec, prec, boff, poff, counters, pflag;
-  CYL_TRY(brec.alloc((size_t)nb * bw.nwords * 8 + 16, s));
-  CYL_TRY(prec.alloc((size_t)np * pw.nwords * 8 + 16, s));
-  CYL_TRY(boff.alloc((size_t)(nbins + 1) * sizeof(int64_t), s));
-  CYL_TRY(poff.alloc((size_t)(nbins + 1) * sizeof(int64_t), s));
-  const int bpart = nkeys == 2 ? bw.hash_word : bw.key_word[0], ppart = nkeys == 2 ? pw.hash_word : pw.key_word[0];
-  CYL_TRY(f8_partition(bw.cols, bw.nwords, bpart, nb, nbins, shift, brec.as<uint64_t>(), boff.as<int64_t>(), s));
-  CYL_TRY(f8_partition(pw.cols, pw.nwords, ppart, np, nbins, shift, prec.as<uint64_t>(), poff.as<int64_t>(), s));
+  Scratch lrec, rrec, loff, roff, counters, pflag, maxbin;
+  CYL_TRY(lrec.alloc((size_t)nl * lw.nwords * 8 + 16, s));
+  CYL_TRY(rrec.alloc((size_t)nr * rw.nwords * 8 + 16, s));
+  CYL_TRY(loff.alloc((size_t)(nbins + 1) * sizeof(int64_t), s));
+  CYL_TRY(roff.alloc((size_t)(nbins + 1) * sizeof(int64_t), s));
+  const int lpart = nkeys == 2 ? lw.hash_word : lw.key_word[0], rpart = nkeys == 2 ? rw.hash_word : rw.key_word[0];
+  CYL_TRY(f8_partition(lw.cols, lw.nwords, lpart, nl, nbins, shift, lrec.as<uint64_t>(), loff.as<int64_t>(), s));
+  CYL_TRY(f8_partition(rw.cols, rw.nwords, rpart, nr, nbins, shift, rrec.as<uint64_t>(), roff.as<int64_t>(), s));
+  CYL_TRY(maxbin.alloc(64, s));
+  CYL_CUDA(cudaMemsetAsync(maxbin.p, 0, 64, s));
+  x_maxbin_kernel<<<x_grid(nbins), 256, 0, s>>>(loff.as<int64_t>(), roff.as<int64_t>(), nbins, maxbin.as<unsigned long long>());
+  CYL_LAUNCH_CHECK();
+  unsigned long long fullest[2] = {0, 0};
+  CYL_CUDA(cudaMemcpyAsync(fullest, maxbin.p, sizeof(fullest), cudaMemcpyDeviceToHost, s));
+  CYL_CUDA(cudaStreamSynchronize(s));
+  bool build_right;
+  if (fullest[0] > (unsigned long long)lcap || fullest[1] > (unsigned long long)rcap) {
+    build_right = fullest[1] < fullest[0];  // some bin overflows shared memory on one side: build from the other
+  } else {
+    switch (join_type) {  // no skew to speak of: the reference's choice
+      case CYL_JOIN_LEFT: build_right = true; break;
+      case CYL_JOIN_RIGHT: build_right = false; break;
+      default: build_right = !(nl <= nr); break;
+    }
+  }
+  const cyl_column_t *bcols = build_right ? rcols : lcols, *pcols = build_right ? lcols : rcols;
+  const int nbc = build_right ? nrcols : nlcols, npc = build_right ? nlcols : nrcols;
+  const int32_t *bkeys = build_right ? rkeys : lkeys;
+  const int64_t nb = build_right ? nr : nl, np = build_right ? nl : nr;
+  XWords &bw = build_right ? rw : lw, &pw = build_right ? lw : rw;
+  Scratch &brec = build_right ? rrec : lrec, &prec = build_right ? lrec : rrec;
+  Scratch &boff = build_right ? roff : loff, &poff = build_right ? loff : roff;
+  const int bpart = build_right ? rpart : lpart, ppart = build_right ? lpart : rpart;
+  const int cap = build_right ? rcap : lcap, nheads = build_right ? rheads : lheads;
+  const size_t smem_bytes = build_right ? rsmem : lsmem;
 
   F8XArgs a;
   memset(&a, 0, sizeof(a));
@@ -451,8 +546,10 @@ int cyl_join_fused(const cyl_column_t *lcols, int32_t nlcols, const int32_t *lke
   a.bucket_word_p = ppart;
   const int32_t ktype = bcols[bkeys[0]].type;
   a.nan_type = (nkeys == 1 && (ktype == CYL_FLOAT || ktype == CYL_DOUBLE)) ? ktype : 0;
-  a.keep_probe = join_type != CYL_JOIN_INNER;
-  a.keep_build = join_type == CYL_JOIN_FULL_OUTER;
+  const bool left_kept = join_type == CYL_JOIN_LEFT || join_type == CYL_JOIN_FULL_OUTER;
+  const bool right_kept = join_type == CYL_JOIN_RIGHT || join_type == CYL_JOIN_FULL_OUTER;
+  a.keep_probe = build_right ? left_kept : right_kept;
+  a.keep_build = build_right ? right_kept : left_kept;
   // output columns: all left columns then all right columns (build_final_table, join_utils.cpp:126-181)
   void *const *bout = build_right ? out_cols + nlcols : out_cols;
   void *const *pout = build_right ? out_cols : out_cols + nlcols;
@@ -479,13 +576,27 @@ int cyl_join_fused(const cyl_column_t *lcols, int32_t nlcols, const int32_t *lke
   CYL_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
   a.out_cursor = counters.as<unsigned long long>();
   a.work_counter = reinterpret_cast<unsigned int *>(counters.as<char>() + 16);
+  Scratch nsl, slice_off, bflag, tickets;
+  CYL_TRY(nsl.alloc((size_t)(nbins + 1) * sizeof(uint32_t), s));
+  CYL_TRY(slice_off.alloc((size_t)(nbins + 2) * sizeof(int64_t), s));
+  x_slices_kernel<<<x_grid(nbins), 256, 0, s>>>(poff.as<int64_t>(), nbins, nsl.as<uint32_t>());
+  CYL_LAUNCH_CHECK();
+  CYL_TRY(exclusive_scan<uint32_t>(nsl.as<uint32_t>(), nbins, slice_off.as<int64_t>(), s));
+  a.slice_off = slice_off.as<int64_t>();
+  if (a.keep_build) {
+    CYL_TRY(bflag.alloc((size_t)nb + 16, s));
+    CYL_CUDA(cudaMemsetAsync(bflag.p, 0, (size_t)nb + 16, s));
+    CYL_TRY(tickets.alloc((size_t)nbins * sizeof(unsigned int), s));
+    CYL_CUDA(cudaMemsetAsync(tickets.p, 0, (size_t)nbins * sizeof(unsigned int), s));
+    a.bflag = bflag.as<uint8_t>();
+    a.bin_ticket = tickets.as<unsigned int>();
+  }
   if (a.keep_probe) {
     CYL_TRY(pflag.alloc((size_t)np + 16, s));
     CYL_CUDA(cudaMemsetAsync(pflag.p, 0, (size_t)np + 16, s));
     a.pflag = pflag.as<uint8_t>();
   }
-  int64_t grid = (int64_t)num_sms() * 2;
-  if (grid > nbins) grid = nbins;
+  const int64_t grid = (int64_t)num_sms() * 2;  // work items are handed out dynamically; their number is only known on the device
   {
     ProfScope ps("fused_join_probe_x", s);
     int rc;

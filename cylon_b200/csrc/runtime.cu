@@ -53,7 +53,11 @@ size_t size_class(size_t bytes) {
 }
 }  // namespace
 
+static std::atomic<long long> g_pool_generation{0};
+long long pool_generation() { return g_pool_generation.load(); }
+
 void pool_trim() {
+  g_pool_generation.fetch_add(1);  // addresses handed to peers (CUDA IPC) may be recycled for other allocations from here on
   std::lock_guard<std::mutex> lk(g_pool_mu);
   for (auto &kv : g_pool_free)
     for (void *p : kv.second) {

@@ -14,7 +14,9 @@
 #include <nccl.h>
 
 #include <cstdlib>
+#include <iterator>
 #include <map>
+#include <set>
 #include <mutex>
 
 #include "../csrc/common.cuh"
@@ -91,7 +93,8 @@ class NcclCommunicator : public net::Communicator {
   // Handles are cached: the allocator recycles the same blocks step after step, so after warm-up nothing is opened.
   Status MapPeerBuffers(void *const *mine, int n, void **peers, bool *all_ok, void *stream) override {
     constexpr int kWords = sizeof(cudaIpcMemHandle_t) / 8;  // 64-byte handle = 8 words
-    std::vector<int64_t> send((size_t)n * kWords), recv((size_t)n * kWords * world_);
+    const int per_rank = n * kWords + 2;                    // + "my handles are fine" + allocator generation
+    std::vector<int64_t> send((size_t)per_rank), recv((size_t)per_rank * world_);
     bool ok = !ipc_broken_;
     for (int i = 0; i < n && ok; i++) {
       cudaIpcMemHandle_t h;
@@ -102,18 +105,47 @@ class NcclCommunicator : public net::Communicator {
       }
       memcpy(&send[(size_t)i * kWords], &h, sizeof(h));
     }
-    RETURN_CYLON_STATUS_IF_FAILED(AllGather(send.data(), n * kWords, recv.data(), stream));
-    for (int r = 0; r < world_ && ok; r++) {
-      for (int i = 0; i < n && ok; i++) {
-        if (r == rank_) {
-          peers[(size_t)r * n + i] = mine[i];
-          continue;
+    send[(size_t)n * kWords] = ok ? 1 : 0;
+    send[(size_t)n * kWords + 1] = (int64_t)cylb::pool_generation();
+    RETURN_CYLON_STATUS_IF_FAILED(AllGather(send.data(), per_rank, recv.data(), stream));
+    if (peer_generation_.size() != (size_t)world_) peer_generation_.assign((size_t)world_, -1);
+    // `any_new` is computed from the gathered data alone, so every rank reaches the same value: it decides whether the
+    // agreement exchange below runs, and a collective must be entered by all ranks or by none.
+    bool any_new = false;
+    for (int r = 0; r < world_; r++) {
+      // A rank that trimmed its allocator since the last exchange may have given the same addresses to other blocks:
+      // every mapping of its memory cached anywhere is closed and opened again from the handles it sends now.
+      const int64_t gen = recv[(size_t)r * per_rank + (size_t)n * kWords + 1];
+      if (peer_generation_[r] != gen) {
+        for (auto it = seen_.begin(); it != seen_.end();) it = it->first == r ? seen_.erase(it) : std::next(it);
+        for (auto it = ipc_cache_.begin(); it != ipc_cache_.end();) {
+          if (it->first.first == r) {
+            cudaIpcCloseMemHandle(it->second);
+            it = ipc_cache_.erase(it);
+          } else {
+            ++it;
+          }
         }
-        std::string key(reinterpret_cast<const char *>(&recv[((size_t)r * n + i) * kWords]), sizeof(cudaIpcMemHandle_t));
+        peer_generation_[r] = gen;
+      }
+      for (int i = 0; i < n; i++) {
+        std::pair<int, std::string> key(r, std::string(reinterpret_cast<const char *>(&recv[(size_t)r * per_rank + (size_t)i * kWords]),
+                                                       sizeof(cudaIpcMemHandle_t)));
+        if (seen_.insert(key).second) any_new = true;
+      }
+    }
+    for (int r = 0; r < world_ && ok; r++) {
+      if (r == rank_) {
+        for (int i = 0; i < n; i++) peers[(size_t)r * n + i] = mine[i];
+        continue;
+      }
+      for (int i = 0; i < n && ok; i++) {
+        std::pair<int, std::string> key(r, std::string(reinterpret_cast<const char *>(&recv[(size_t)r * per_rank + (size_t)i * kWords]),
+                                                       sizeof(cudaIpcMemHandle_t)));
         auto it = ipc_cache_.find(key);
         if (it == ipc_cache_.end()) {
           cudaIpcMemHandle_t h;
-          memcpy(&h, key.data(), sizeof(h));
+          memcpy(&h, key.second.data(), sizeof(h));
           void *p = nullptr;
           if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
             (void)cudaGetLastError();
@@ -125,12 +157,20 @@ class NcclCommunicator : public net::Communicator {
         peers[(size_t)r * n + i] = it->second;
       }
     }
-    // agree: one rank failing means nobody uses peer stores
-    int64_t mine_ok = ok ? 1 : 0;
-    std::vector<int64_t> oks((size_t)world_);
-    RETURN_CYLON_STATUS_IF_FAILED(AllGather(&mine_ok, 1, oks.data(), stream));
-    *all_ok = true;
-    for (int64_t v : oks) *all_ok = *all_ok && v != 0;
+    // Agreement: one rank failing to map means nobody uses peer stores. Mapping can only fail for a handle that is new,
+    // so the exchange is skipped when every handle of this call was seen before (the allocator recycles the same blocks
+    // step after step) and every rank had reported its own handles fine.
+    bool all_fine = true;
+    for (int r = 0; r < world_; r++) all_fine = all_fine && recv[(size_t)r * per_rank + (size_t)n * kWords] != 0;
+    if (any_new || !all_fine || ipc_broken_) {
+      int64_t mine_ok = ok ? 1 : 0;
+      std::vector<int64_t> oks((size_t)world_);
+      RETURN_CYLON_STATUS_IF_FAILED(AllGather(&mine_ok, 1, oks.data(), stream));
+      *all_ok = true;
+      for (int64_t v : oks) *all_ok = *all_ok && v != 0;
+    } else {
+      *all_ok = true;
+    }
     if (!*all_ok) ipc_broken_ = true;
     return Status::OK();
   }
@@ -198,7 +238,9 @@ class NcclCommunicator : public net::Communicator {
   int rank_, world_;
   void *barrier_word_ = nullptr;
   bool ipc_broken_ = false;
-  std::map<std::string, void *> ipc_cache_;
+  std::map<std::pair<int, std::string>, void *> ipc_cache_;  // (peer rank, IPC handle) -> mapping in this process
+  std::vector<int64_t> peer_generation_;                      // allocator generation each peer reported last
+  std::set<std::pair<int, std::string>> seen_;                // every (rank, handle) exchanged so far, identical on all ranks
 };
 
 thread_local std::string g_ctx_error;

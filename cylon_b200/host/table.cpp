@@ -207,8 +207,10 @@ Status Join(std::shared_ptr<Table> &left, std::shared_ptr<Table> &right, const j
       const int64_t nl = left->Rows(), nr = right->Rows();
       const bool left_null = jt == CYL_JOIN_RIGHT || jt == CYL_JOIN_FULL_OUTER;
       const bool right_null = jt == CYL_JOIN_LEFT || jt == CYL_JOIN_FULL_OUTER;
+      // optimistic result size: one partner per row for INNER; an outer join also keeps every unmatched row of its
+      // preserved side(s), so all rows of both tables (exact when keys are unique on one side, the usual shape)
       int64_t capacity = std::max(nl, nr) + std::max(nl, nr) / 8 + 1024;
-      if (jt == CYL_JOIN_FULL_OUTER) capacity = nl + nr + 1024;
+      if (jt != CYL_JOIN_INNER) capacity = nl + nr + 1024;
       for (int attempt = 0; attempt < 2; attempt++) {
         std::vector<std::shared_ptr<Column>> cols;
         std::vector<void *> outs;
