@@ -15,7 +15,7 @@ from .capi import (BINARY, COUNT, DOUBLE, FIXED_SIZE_BINARY, FLOAT, FULL_OUTER, 
 
 _JOIN_TYPES = {"inner": INNER, "left": LEFT, "right": RIGHT, "outer": FULL_OUTER, "fullouter": FULL_OUTER, "full_outer": FULL_OUTER}
 _ALGOS = {"sort": SORT, "hash": HASH}
-_AGGS = {"sum": SUM, "min": MIN, "max": MAX, "count": COUNT}
+_AGGS = {"sum": SUM, "min": MIN, "max": MAX, "count": COUNT, "mean": 4, "var": 5, "std": 8, "stddev": 8}  # AggregationOpId values
 
 
 def nccl_unique_id():

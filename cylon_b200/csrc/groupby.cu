@@ -94,6 +94,8 @@ __host__ __device__ inline T dec_ordered(typename AccWord<T>::type w) {
   }
 }
 
+constexpr int kAggSumSq = 100;  // internal: sum of squares (VAR / STDDEV)
+
 template <typename W>
 __global__ void fill_words_kernel(W *__restrict__ p, int64_t n, W v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
@@ -106,7 +108,14 @@ __global__ void __launch_bounds__(256) aggregate_kernel(const T *__restrict__ v,
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t g = gid[i];
     const T x = v[i];
-    if constexpr (OP == CYL_AGG_SUM) {
+    if constexpr (OP == kAggSumSq) {  // VarianceKernel's first state: sum of value * value in the column's own type
+      if constexpr (std::is_floating_point<T>::value) {
+        atomicAdd(reinterpret_cast<T *>(acc) + g, x * x);
+      } else {
+        const W w = (W)(typename std::make_unsigned<T>::type)x;  // the product wraps like T's after truncation whatever the sign
+        atomicAdd(acc + g, w * w);
+      }
+    } else if constexpr (OP == CYL_AGG_SUM) {
       if constexpr (std::is_floating_point<T>::value) {
         atomicAdd(reinterpret_cast<T *>(acc) + g, x);
       } else if constexpr (std::is_signed<T>::value) {
@@ -170,13 +179,81 @@ static int aggregate_typed(const void *data, const int64_t *gid, int64_t n, int6
   return CYL_OK;
 }
 
+// MeanKernel / VarianceKernel finalisers (aggregate_kernels.hpp:344-405): sum, sum of squares (both in T) and count -> result
+template <typename T>
+__global__ void finalize_mean_kernel(const typename AccWord<T>::type *sum, const unsigned long long *cnt, int64_t g, T *out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g; i += (int64_t)gridDim.x * blockDim.x) {
+    T s;
+    if constexpr (std::is_floating_point<T>::value) s = reinterpret_cast<const T *>(sum)[i];
+    else s = (T)sum[i];
+    const long long c = (long long)cnt[i];
+    out[i] = c ? (T)(s / c) : (T)0;  // T / int64 with the usual arithmetic conversions, stored as T
+  }
+}
+
+template <typename T>
+__global__ void finalize_var_kernel(const typename AccWord<T>::type *sumsq, const typename AccWord<T>::type *sum, const unsigned long long *cnt,
+                                    int64_t g, int do_std, double *out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g; i += (int64_t)gridDim.x * blockDim.x) {
+    T s, q;
+    if constexpr (std::is_floating_point<T>::value) {
+      s = reinterpret_cast<const T *>(sum)[i];
+      q = reinterpret_cast<const T *>(sumsq)[i];
+    } else {
+      s = (T)sum[i];
+      q = (T)sumsq[i];
+    }
+    const long long c = (long long)cnt[i];
+    double r = 0;
+    if (c > 1) {
+      const double mean = (double)s / (double)c, mean_sq = (double)q / (double)c;
+      r = (double)c * (mean_sq - mean * mean) / (double)(c - 1);  // ddof = 1: VarKernelOptions' default (:72)
+      if (do_std) r = sqrt(r);
+    }
+    out[i] = r;
+  }
+}
+
+template <typename T>
+static int aggregate_moments(int op, const void *data, const int64_t *gid, int64_t n, int64_t g, void *out, cudaStream_t s) {
+  using W = typename AccWord<T>::type;
+  Scratch sum, sq, cnt;
+  CYL_TRY(sum.alloc((size_t)(g + 1) * sizeof(W), s));
+  CYL_TRY(cnt.alloc((size_t)(g + 1) * sizeof(unsigned long long), s));
+  CYL_CUDA(cudaMemsetAsync(sum.p, 0, (size_t)(g + 1) * sizeof(W), s));
+  CYL_CUDA(cudaMemsetAsync(cnt.p, 0, (size_t)(g + 1) * sizeof(unsigned long long), s));
+  const bool var = op != CYL_AGG_MEAN;
+  if (var) {
+    CYL_TRY(sq.alloc((size_t)(g + 1) * sizeof(W), s));
+    CYL_CUDA(cudaMemsetAsync(sq.p, 0, (size_t)(g + 1) * sizeof(W), s));
+  }
+  if (n > 0) {
+    ProfScope ps("groupby_aggregate", s);
+    aggregate_kernel<T, CYL_AGG_SUM><<<grid1d(n), 256, 0, s>>>(static_cast<const T *>(data), gid, n, sum.as<W>());
+    CYL_LAUNCH_CHECK();
+    count_kernel<<<grid1d(n), 256, 0, s>>>(gid, n, cnt.as<unsigned long long>());
+    CYL_LAUNCH_CHECK();
+    if (var) {
+      aggregate_kernel<T, kAggSumSq><<<grid1d(n), 256, 0, s>>>(static_cast<const T *>(data), gid, n, sq.as<W>());
+      CYL_LAUNCH_CHECK();
+    }
+  }
+  if (g > 0) {
+    if (var) finalize_var_kernel<T><<<grid1d(g), 256, 0, s>>>(sq.as<W>(), sum.as<W>(), cnt.as<unsigned long long>(), g, op == CYL_AGG_STDDEV, static_cast<double *>(out));
+    else finalize_mean_kernel<T><<<grid1d(g), 256, 0, s>>>(sum.as<W>(), cnt.as<unsigned long long>(), g, static_cast<T *>(out));
+    CYL_LAUNCH_CHECK();
+  }
+  return CYL_OK;
+}
+
 template <typename T>
 static int aggregate_op(int op, const void *data, const int64_t *gid, int64_t n, int64_t g, void *out, cudaStream_t s) {
+  if (op == CYL_AGG_MEAN || op == CYL_AGG_VAR || op == CYL_AGG_STDDEV) return aggregate_moments<T>(op, data, gid, n, g, out, s);
   switch (op) {
     case CYL_AGG_SUM: return aggregate_typed<T, CYL_AGG_SUM>(data, gid, n, g, out, s);
     case CYL_AGG_MIN: return aggregate_typed<T, CYL_AGG_MIN>(data, gid, n, g, out, s);
     case CYL_AGG_MAX: return aggregate_typed<T, CYL_AGG_MAX>(data, gid, n, g, out, s);
-    default: return fail(CYL_NotImplemented, "cyl_aggregate: aggregation op %d is not on the accelerated path (SUM/MIN/MAX/COUNT only)", op);
+    default: return fail(CYL_NotImplemented, "cyl_aggregate: aggregation op %d is not on the accelerated path (NUNIQUE / QUANTILE are not)", op);
   }
 }
 

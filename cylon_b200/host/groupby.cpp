@@ -19,8 +19,8 @@ Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_
   RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*table, keys, "HashGroupBy"));
   for (const auto &a : aggregations) {
     if (a.first < 0 || a.first >= table->Columns()) return Status(Code::IndexError, "HashGroupBy: aggregate column out of range");
-    if (a.second != compute::SUM && a.second != compute::MIN && a.second != compute::MAX && a.second != compute::COUNT)
-      return Status(Code::NotImplemented, "HashGroupBy: only SUM/MIN/MAX/COUNT run on the GPU path");
+    if (a.second == compute::NUNIQUE || a.second == compute::QUANTILE || (int)a.second < 0 || (int)a.second > (int)compute::STDDEV)
+      return Status(Code::NotImplemented, "HashGroupBy: NUNIQUE / QUANTILE do not run on the GPU path");
   }
   auto ctx = table->GetContext();
   void *stream = ctx->GetStream();
@@ -41,7 +41,7 @@ Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_
         at = (int32_t)values.size() - 1;
       }
       agg_value.push_back(at);
-      agg_op.push_back(a.second == compute::SUM ? CYL_AGG_SUM : a.second == compute::MIN ? CYL_AGG_MIN : a.second == compute::MAX ? CYL_AGG_MAX : CYL_AGG_COUNT);
+      agg_op.push_back((int32_t)a.second);  // AggregationOpId and cyl_agg_op_t number alike; the fused path takes the first four
     }
     if (n > 0 && cyl_groupby_fused_supported(&key, values.data(), (int32_t)values.size(), agg_value.data(), agg_op.data(), (int32_t)agg_op.size())) {
       int64_t capacity = std::min<int64_t>(n, n / 4 + (1 << 20));
@@ -99,18 +99,13 @@ Status HashGroupBy(const std::shared_ptr<Table> &table, const std::vector<int32_
   for (const auto &a : aggregations) {
     const auto &src = table->GetColumn(a.first);
     const bool count = a.second == compute::COUNT;
-    const int32_t type = count ? (int32_t)CYL_INT64 : src->type();
-    const int32_t width = count ? 8 : src->byte_width();
+    const bool as_double = a.second == compute::VAR || a.second == compute::STDDEV;  // KernelTraits<VAR,T>::ResultT = double
+    const int32_t type = count ? (int32_t)CYL_INT64 : (as_double ? (int32_t)CYL_DOUBLE : src->type());
+    const int32_t width = (count || as_double) ? 8 : src->byte_width();
     std::shared_ptr<Column> col;
     RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(std::string(compute::AggregationPrefix(a.second)) + src->name(), type, width, groups,
                                                    groups * (int64_t)width, false, stream, &col));
-    int op = 0;
-    switch (a.second) {
-      case compute::SUM: op = CYL_AGG_SUM; break;
-      case compute::MIN: op = CYL_AGG_MIN; break;
-      case compute::MAX: op = CYL_AGG_MAX; break;
-      default: op = CYL_AGG_COUNT; break;
-    }
+    const int op = (int)a.second;
     CYL_RETURN_IF_FAILED(cyl_aggregate(&src->desc(), gid.as<int64_t>(), groups, op, col->mutable_data(), stream));
     cols.push_back(col);
   }
@@ -144,11 +139,14 @@ Status DistributedHashGroupBy(std::shared_ptr<Table> &table, const std::vector<i
   for (size_t i = 0; i < aggregate_cols.size(); i++) aggs.emplace_back((int32_t)(index_cols.size() + i), aggregate_ops[i]);
 
   const int world = table->GetContext()->GetWorldSize();
-  for (auto op : aggregate_ops)  // refuse before anything is shuffled (the reference finds out after its shuffle, hash_groupby.cpp:217-248)
-    if (op != compute::SUM && op != compute::MIN && op != compute::MAX && op != compute::COUNT)
-      return Status(Code::NotImplemented, "DistributedHashGroupBy: only SUM/MIN/MAX/COUNT run on the GPU path");
+  bool basic_ops = true;  // SUM / MIN / MAX / COUNT only: partial results can be combined after the shuffle
+  for (auto op : aggregate_ops) {  // refuse before anything is shuffled (the reference finds out after its shuffle, hash_groupby.cpp:217-248)
+    if (op == compute::NUNIQUE || op == compute::QUANTILE || (int)op < 0 || (int)op > (int)compute::STDDEV)
+      return Status(Code::NotImplemented, "DistributedHashGroupBy: NUNIQUE / QUANTILE do not run on the GPU path");
+    basic_ops = basic_ops && (op == compute::SUM || op == compute::MIN || op == compute::MAX || op == compute::COUNT);
+  }
   std::shared_ptr<Table> local;
-  if (world > 1 && !is_associative(aggregate_ops) && table->GetContext()->GetConfig("cylon.groupby.preaggregate", "1") != "0") {
+  if (world > 1 && basic_ops && !is_associative(aggregate_ops) && table->GetContext()->GetConfig("cylon.groupby.preaggregate", "1") != "0") {
     // COUNT among the operations. The reference then ships every raw row through the shuffle (groupby.cpp:60-77: it only
     // pre-aggregates when all operations are in {SUM, MIN, MAX}). Here the rows are still reduced locally first and the
     // partial COUNTs are SUMmed after the shuffle, so only one row per (rank, group) crosses NVLink; the result columns

@@ -1,6 +1,6 @@
 // cylon::compute::AggregationOpId -- same enumerators and values as the reference
-// (cpp/src/cylon/compute/aggregate_kernels.hpp:40-50). SUM/MIN/MAX/COUNT run on the GPU; the others are outside the
-// accelerated path and return Code::NotImplemented.
+// (cpp/src/cylon/compute/aggregate_kernels.hpp:40-50). SUM / MIN / MAX / COUNT / MEAN / VAR / STDDEV run on the GPU; NUNIQUE and
+// QUANTILE are outside the accelerated path and return Code::NotImplemented.
 #pragma once
 namespace cylon {
 namespace compute {

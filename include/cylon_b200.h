@@ -227,8 +227,10 @@ int cyl_groupby_hash(const cyl_column_t *keys /* host array */, int32_t nkeys, i
                      int64_t *num_groups /* host out */, void *stream);
 /* out[g] = op over { col[i] : gid[i] == g }. out holds num_groups values of the column's type (SUM/MIN/MAX) or int64
  * (COUNT). SUM wraps in the column's C type, MIN starts at numeric_limits<T>::max(), MAX at numeric_limits<T>::min()
- * (DBL_MIN/FLT_MIN for floating point -- the reference's behaviour). col is a host pointer to one descriptor.
- * Replaces aggregate<op,T> (groupby/hash_groupby.cpp:142-201) + compute/aggregate_kernels.hpp:410-485. */
+ * (DBL_MIN/FLT_MIN for floating point -- the reference's behaviour). MEAN: sum (in the column's type) / count with C++'s
+ * conversions, stored in the column's type; VAR / STDDEV: double, from sum and sum of squares accumulated in the
+ * column's type, ddof = 1 (VarKernelOptions' default), 0 for single-row groups. col is a host pointer to one descriptor.
+ * Replaces aggregate<op,T> (groupby/hash_groupby.cpp:142-201) + compute/aggregate_kernels.hpp:344-405,410-485. */
 int cyl_aggregate(const cyl_column_t *col /* host */, const int64_t *gid, int64_t num_groups, int32_t op, void *out, void *stream);
 /* Fused fast path of HashGroupBy for ONE 8-byte key column (int64 / uint64 / double / date64 / timestamp / time64) and 8-byte
  * value columns (int64 / uint64 / double), all without validity bitmaps, at most 3 distinct value columns and 4 aggregates:

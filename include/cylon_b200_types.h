@@ -79,7 +79,10 @@ typedef enum cyl_join_type { CYL_JOIN_INNER = 0, CYL_JOIN_LEFT = 1, CYL_JOIN_RIG
 typedef enum cyl_join_algorithm { CYL_JOIN_SORT = 0, CYL_JOIN_HASH = 1 } cyl_join_algorithm_t;
 
 /* cylon::compute::AggregationOpId (cpp/src/cylon/compute/aggregate_kernels.hpp:40-50). */
-typedef enum cyl_agg_op { CYL_AGG_SUM = 0, CYL_AGG_MIN = 1, CYL_AGG_MAX = 2, CYL_AGG_COUNT = 3 } cyl_agg_op_t;
+typedef enum cyl_agg_op {
+  CYL_AGG_SUM = 0, CYL_AGG_MIN = 1, CYL_AGG_MAX = 2, CYL_AGG_COUNT = 3,
+  CYL_AGG_MEAN = 4, CYL_AGG_VAR = 5, CYL_AGG_STDDEV = 8 /* 6 = NUNIQUE, 7 = QUANTILE: not on the GPU path */
+} cyl_agg_op_t;
 
 /* Row-set operations of cpp/src/cylon/table.cpp:531-721,923-982. */
 typedef enum cyl_setop { CYL_SETOP_UNION = 0, CYL_SETOP_SUBTRACT = 1, CYL_SETOP_INTERSECT = 2, CYL_SETOP_UNIQUE = 3 } cyl_setop_t;

@@ -9,6 +9,7 @@
 #include "oracle.h"
 
 #include <float.h>
+#include <math.h>
 #include <limits.h>
 #include <stdlib.h>
 #include <string.h>
@@ -537,8 +538,56 @@ int orc_groupby_ids(const cyl_column_t *keys, int32_t nkeys, int64_t nrows, int6
     }                                                                                         \
   } while (0)
 
+/* MeanKernel / VarianceKernel (VAR, STDDEV), aggregate_kernels.hpp:344-405. States accumulate in the column's own C type
+ * (integers wrap, float sums stay float); MEAN divides sum (T) by count (int64) with C++'s usual conversions and stores T;
+ * VAR / STDDEV finish in double with ddof = 1, the default of VarKernelOptions (:72), and 0 for a single-row group. */
+#define MEANVAR_LOOP(T)                                                                                         \
+  do {                                                                                                          \
+    const T *v = (const T *)col->data;                                                                          \
+    T *sum = (T *)calloc((size_t)num_groups + 1, sizeof(T)), *sq = (T *)calloc((size_t)num_groups + 1, sizeof(T)); \
+    int64_t *cnt = (int64_t *)calloc((size_t)num_groups + 1, sizeof(int64_t));                                  \
+    if (!sum || !sq || !cnt) return CYL_OutOfMemory;                                                            \
+    for (int64_t i = 0; i < n; i++) {                                                                           \
+      sq[gid[i]] += v[i] * v[i];                                                                                \
+      sum[gid[i]] += v[i];                                                                                      \
+      cnt[gid[i]] += 1;                                                                                         \
+    }                                                                                                           \
+    for (int64_t g = 0; g < num_groups; g++) {                                                                  \
+      if (op == ORC_AGG_MEAN) {                                                                                 \
+        ((T *)out)[g] = cnt[g] ? (T)(sum[g] / cnt[g]) : (T)0;                                                   \
+      } else {                                                                                                  \
+        double r = 0;                                                                                           \
+        if (cnt[g] > 1) {                                                                                       \
+          double mean = (double)sum[g] / (double)cnt[g], mean_sq = (double)sq[g] / (double)cnt[g];              \
+          r = (double)cnt[g] * (mean_sq - mean * mean) / (double)(cnt[g] - 1);                                  \
+          if (op == ORC_AGG_STDDEV) r = sqrt(r);                                                                \
+        }                                                                                                       \
+        ((double *)out)[g] = r;                                                                                 \
+      }                                                                                                         \
+    }                                                                                                           \
+    free(sum); free(sq); free(cnt);                                                                             \
+  } while (0)
+
+enum { ORC_AGG_MEAN = 4, ORC_AGG_VAR = 5, ORC_AGG_STDDEV = 8 }; /* AggregationOpId, aggregate_kernels.hpp:40-50 */
+
 int orc_aggregate(const cyl_column_t *col, const int64_t *gid, int64_t num_groups, int32_t op, void *out) {
   const int64_t n = col->length;
+  if (op == ORC_AGG_MEAN || op == ORC_AGG_VAR || op == ORC_AGG_STDDEV) {
+    switch (col->type) {
+      case CYL_UINT8: MEANVAR_LOOP(uint8_t); break;
+      case CYL_INT8: MEANVAR_LOOP(int8_t); break;
+      case CYL_UINT16: MEANVAR_LOOP(uint16_t); break;
+      case CYL_INT16: MEANVAR_LOOP(int16_t); break;
+      case CYL_UINT32: MEANVAR_LOOP(uint32_t); break;
+      case CYL_INT32: MEANVAR_LOOP(int32_t); break;
+      case CYL_UINT64: MEANVAR_LOOP(uint64_t); break;
+      case CYL_INT64: MEANVAR_LOOP(int64_t); break;
+      case CYL_FLOAT: MEANVAR_LOOP(float); break;
+      case CYL_DOUBLE: MEANVAR_LOOP(double); break;
+      default: return CYL_ExecutionError;
+    }
+    return CYL_OK;
+  }
   if (op == CYL_AGG_COUNT) { /* CountKernel, aggregate_kernels.hpp:432-447: counts every row */
     int64_t *o = (int64_t *)out;
     for (int64_t g = 0; g < num_groups; g++) o[g] = 0;

@@ -24,6 +24,7 @@ DATE32, DATE64, TIMESTAMP, TIME32, TIME64 = 16, 17, 18, 19, 20
 INNER, LEFT, RIGHT, FULL_OUTER = 0, 1, 2, 3
 SORT, HASH = 0, 1
 SUM, MIN, MAX, COUNT = 0, 1, 2, 3
+MEAN, VAR, STDDEV = 4, 5, 8  # AggregationOpId (aggregate_kernels.hpp:40-50); NUNIQUE = 6 and QUANTILE = 7 are not restated
 UNION, SUBTRACT, INTERSECT, UNIQUE = 0, 1, 2, 3
 
 _NP2TYPE = {np.dtype(k): v for k, v in {
@@ -32,7 +33,7 @@ _NP2TYPE = {np.dtype(k): v for k, v in {
 _TYPE2NP = {v: k for k, v in _NP2TYPE.items()}
 _TYPE2NP.update({DATE32: np.dtype("int32"), DATE64: np.dtype("int64"), TIMESTAMP: np.dtype("int64"),
                  TIME32: np.dtype("int32"), TIME64: np.dtype("int64")})
-AGG_PREFIX = {SUM: "sum_", MIN: "min_", MAX: "max_", COUNT: "count_"}  # aggregate_kernels.hpp:186-260
+AGG_PREFIX = {SUM: "sum_", MIN: "min_", MAX: "max_", COUNT: "count_", MEAN: "mean_", VAR: "var_", STDDEV: "std_"}  # aggregate_kernels.hpp:186-260
 
 
 class CylColumn(C.Structure):
@@ -281,7 +282,7 @@ def groupby_ids(keys):
 
 
 def aggregate(column, gid, num_groups, op):
-    dt = np.dtype("int64") if op == COUNT else _TYPE2NP[column.type]
+    dt = np.dtype("int64") if op == COUNT else (np.dtype("float64") if op in (VAR, STDDEV) else _TYPE2NP[column.type])
     out = np.zeros(max(1, num_groups), dtype=dt)
     arr, _k = _to_c([column])
     gid = np.ascontiguousarray(gid, dtype=np.int64)
@@ -421,7 +422,7 @@ def hash_groupby(table, idx_cols, aggs):
     for ci, op in aggs:
         vals = aggregate(table[ci], gid, g, op)
         c = col(vals)
-        if op != COUNT:
+        if op not in (COUNT, VAR, STDDEV):
             c.type = table[ci].type
         c.name = AGG_PREFIX[op] + table[ci].name
         out.append(c)

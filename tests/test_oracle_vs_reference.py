@@ -328,3 +328,20 @@ def test_float_key_identity_row_sets(ncols):
     full, _ = _special_tables(False)
     ref = pyref.dist_op(pyref.DIST_GROUPBY, [full], p1=[0], p2=[1, orc.SUM, 1, orc.COUNT])[0]
     assert _bit_rows(orc.hash_groupby(full, [0], [(1, orc.SUM), (1, orc.COUNT)])) == _bit_rows(ref)
+
+
+@pytest.mark.skipif(not pyref.dist_available(), reason="table operators of the reference not built")
+@pytest.mark.parametrize("dt", ["float64", "float32", "int64", "int32", "uint16", "int8", "uint8"])
+def test_mean_var_stddev_match_reference(dt):
+    """MeanKernel / VarianceKernel (aggregate_kernels.hpp:344-405) through the reference's HashGroupBy: result types, ddof = 1,
+    states in the column's own type (the small integer types wrap)."""
+    rng = np.random.default_rng(len(dt))
+    k = rng.integers(0, 50, 5000).astype(np.int64)
+    v = rng.integers(0, 100, 5000).astype(dt)
+    t = [orc.col(k, name="c0"), orc.col(v, name="c1")]
+    for op in (orc.MEAN, orc.VAR, orc.STDDEV):
+        a = orc.hash_groupby(t, [0], [(1, op)])
+        b = pyref.dist_op(pyref.DIST_GROUPBY, [t], p1=[0], p2=[1, op])[0]
+        assert [c.name for c in a] == [c.name for c in b]
+        assert np.array_equal(a[0].data, b[0].data) and a[1].data.dtype == b[1].data.dtype
+        assert np.allclose(a[1].data, b[1].data, rtol=1e-12, atol=0, equal_nan=True)
