@@ -27,10 +27,13 @@ def nccl_unique_id():
 class CylonContext:
     """CylonContext(config=None, distributed=False) of pycylon; distributed contexts take the NCCL bootstrap."""
 
-    def __init__(self, device=0, distributed=False, rank=0, world_size=1, nccl_id=None):
+    def __init__(self, device=0, distributed=False, rank=0, world_size=1, nccl_id=None, thread_group=None):
         self._h = C.c_void_p()
         self._stream = None
-        if distributed:
+        if thread_group is not None:  # ranks as threads of this process (include/cylon_b200_api.h: cylon_context_init_threads)
+            check(lib().cylon_context_init_threads(str(thread_group).encode(), C.c_int32(rank), C.c_int32(world_size), C.c_int32(device),
+                                                   C.byref(self._h)))
+        elif distributed:
             if nccl_id is None or len(nccl_id) != 128:
                 raise ValueError("distributed context needs the 128-byte NCCL unique id created on rank 0")
             check(lib().cylon_context_init_distributed(C.c_int32(rank), C.c_int32(world_size), C.c_int32(device),

@@ -13,6 +13,7 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <condition_variable>
 #include <cstdlib>
 #include <iterator>
 #include <map>
@@ -243,6 +244,104 @@ class NcclCommunicator : public net::Communicator {
   std::set<std::pair<int, std::string>> seen_;                // every (rank, handle) exchanged so far, identical on all ranks
 };
 
+// ---- ranks as threads of one process (net::ThreadConfig) ---------------------------------------------------------------
+struct ThreadGroup {
+  explicit ThreadGroup(int world) : world(world), gathered((size_t)world), exchanges((size_t)world), pointers((size_t)world) {}
+  const int world;
+  std::mutex mu;
+  std::condition_variable cv;
+  int waiting = 0;
+  long long generation = 0;
+  std::vector<std::vector<int64_t>> gathered;                                  // AllGather contributions by rank
+  std::vector<const std::vector<net::Communicator::Exchange> *> exchanges;     // AllToAllV descriptors by rank
+  std::vector<std::vector<void *>> pointers;                                   // MapPeerBuffers contributions by rank
+  void Barrier() {
+    std::unique_lock<std::mutex> lk(mu);
+    const long long gen = generation;
+    if (++waiting == world) {
+      waiting = 0;
+      generation++;
+      cv.notify_all();
+    } else {
+      cv.wait(lk, [&] { return generation != gen; });
+    }
+  }
+};
+
+std::shared_ptr<ThreadGroup> FindThreadGroup(const std::string &name, int world) {
+  static std::mutex mu;
+  static std::map<std::string, std::weak_ptr<ThreadGroup>> groups;
+  std::lock_guard<std::mutex> lk(mu);
+  auto g = groups[name].lock();
+  if (!g || g->world != world) {
+    g = std::make_shared<ThreadGroup>(world);
+    groups[name] = g;
+  }
+  return g;
+}
+
+class ThreadCommunicator : public net::Communicator {
+ public:
+  ThreadCommunicator(std::shared_ptr<ThreadGroup> group, int rank) : g_(std::move(group)), rank_(rank) {}
+  int GetRank() const override { return rank_; }
+  int GetWorldSize() const override { return g_->world; }
+  net::CommType GetCommType() const override { return net::CommType::THREADS; }
+  void Barrier() override { g_->Barrier(); }
+  void Finalize() override {}
+
+  Status AllGather(const int64_t *send, int n, int64_t *recv, void *) override {
+    g_->gathered[(size_t)rank_].assign(send, send + n);
+    g_->Barrier();  // every contribution is in place
+    for (int r = 0; r < g_->world; r++) memcpy(recv + (size_t)r * n, g_->gathered[(size_t)r].data(), (size_t)n * 8);
+    g_->Barrier();  // everybody has read before anybody overwrites
+    return Status::OK();
+  }
+
+  // Every rank publishes its descriptors once its send buffers are complete, then PULLS its slices out of the peers'
+  // buffers with device-to-device copies on its own stream.
+  Status AllToAllV(const std::vector<Exchange> &ex, void *stream) override {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
+    g_->exchanges[(size_t)rank_] = &ex;
+    g_->Barrier();
+    cudaError_t err = cudaSuccess;
+    for (int p = 0; p < g_->world && err == cudaSuccess; p++) {
+      const auto &theirs = *g_->exchanges[(size_t)p];
+      for (size_t e = 0; e < ex.size() && err == cudaSuccess; e++) {
+        const int64_t bytes = ex[e].recv_bytes[(size_t)p];
+        if (bytes <= 0) continue;
+        err = cudaMemcpyAsync(static_cast<char *>(ex[e].recv) + ex[e].recv_off[(size_t)p],
+                              static_cast<const char *>(theirs[e].send) + theirs[e].send_off[(size_t)rank_], (size_t)bytes, cudaMemcpyDefault, s);
+      }
+    }
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+    g_->Barrier();  // all pulls are done: send buffers may be released
+    if (err != cudaSuccess) return Status(Code::ExecutionError, std::string("thread all-to-all: ") + cudaGetErrorString(err));
+    return Status::OK();
+  }
+
+  Status StreamBarrier(void *stream) override {
+    CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    g_->Barrier();
+    return Status::OK();
+  }
+
+  // same process: a peer's allocation is addressable as it is (same device, or peer access / unified addressing across devices)
+  Status MapPeerBuffers(void *const *mine, int n, void **peers, bool *all_ok, void *) override {
+    g_->pointers[(size_t)rank_].assign(mine, mine + n);
+    g_->Barrier();
+    for (int r = 0; r < g_->world; r++)
+      for (int i = 0; i < n; i++) peers[(size_t)r * n + i] = g_->pointers[(size_t)r][(size_t)i];
+    g_->Barrier();
+    *all_ok = true;
+    return Status::OK();
+  }
+
+ private:
+  std::shared_ptr<ThreadGroup> g_;
+  int rank_;
+};
+
 thread_local std::string g_ctx_error;
 
 }  // namespace
@@ -276,8 +375,23 @@ std::shared_ptr<CylonContext> CylonContext::Init(int device) {
 }
 
 std::shared_ptr<CylonContext> CylonContext::InitDistributed(const std::shared_ptr<net::CommConfig> &config) {
+  if (config && config->Type() == net::CommType::THREADS) {
+    auto tc = std::static_pointer_cast<net::ThreadConfig>(config);
+    if (tc->world_size < 1 || tc->rank < 0 || tc->rank >= tc->world_size) {
+      g_ctx_error = "InitDistributed: ThreadConfig rank / world size out of range";
+      return nullptr;
+    }
+    if (cyl_init(tc->device) != CYL_OK) {
+      g_ctx_error = cyl_last_error();
+      return nullptr;
+    }
+    auto ctx = std::make_shared<CylonContext>(true);
+    ctx->device = tc->device;
+    ctx->communicator = std::make_shared<ThreadCommunicator>(FindThreadGroup(tc->group, tc->world_size), tc->rank);
+    return ctx;
+  }
   if (!config || config->Type() != net::CommType::NCCL) {
-    g_ctx_error = "InitDistributed: only CommType::NCCL is implemented (pass a cylon::net::NcclConfig)";
+    g_ctx_error = "InitDistributed: pass a cylon::net::NcclConfig (one process per GPU) or a cylon::net::ThreadConfig (ranks as threads)";
     return nullptr;
   }
   auto nc = std::static_pointer_cast<net::NcclConfig>(config);

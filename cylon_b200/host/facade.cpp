@@ -68,6 +68,13 @@ int cylon_context_init_distributed(int32_t rank, int32_t world_size, int32_t dev
   return CYL_OK;
 }
 
+int cylon_context_init_threads(const char *group, int32_t rank, int32_t world_size, int32_t device, cylon_context_t **out) {
+  auto ctx = cylon::CylonContext::InitDistributed(cylon::net::ThreadConfig::Make(group ? group : "", rank, world_size, device));
+  if (!ctx) return cylb::fail(CYL_ExecutionError, "%s", cylon::CylonContext::LastError().c_str());
+  *out = new cylon_context{ctx};
+  return CYL_OK;
+}
+
 int cylon_context_set_stream(cylon_context_t *c, void *stream) {
   c->ctx->SetStream(stream);
   return CYL_OK;

@@ -15,7 +15,7 @@
 namespace cylon {
 namespace net {
 
-enum CommType { LOCAL = 0, MPI, TCP, UCX, NCCL };
+enum CommType { LOCAL = 0, MPI, TCP, UCX, NCCL, THREADS };
 
 class CommConfig {
  public:
@@ -39,6 +39,23 @@ class NcclConfig : public CommConfig {
   CommType Type() override { return CommType::NCCL; }
   int rank, world_size, device;
   NcclUniqueId id;
+};
+
+// Ranks as host threads of ONE process (each with its own CylonContext and stream, on the same or on different GPUs):
+// every thread passes the same group name and world size and its own rank. Counts travel through host memory, payloads as
+// device-to-device copies, and the peer-store shuffle writes straight into the other threads' buffers. It exists so that
+// everything above the transport -- partition plans, count exchange, offsets, validity and variable-width packing, the
+// Distributed* operators -- can be exercised at world > 1 on a box with a single GPU (tests/test_gpu_thread_ranks.py);
+// NCCL itself is covered by tests/test_gpu_distributed.py on multi-GPU boxes.
+class ThreadConfig : public CommConfig {
+ public:
+  ThreadConfig(std::string group, int rank, int world_size, int device) : group(std::move(group)), rank(rank), world_size(world_size), device(device) {}
+  static std::shared_ptr<ThreadConfig> Make(const std::string &group, int rank, int world_size, int device) {
+    return std::make_shared<ThreadConfig>(group, rank, world_size, device);
+  }
+  CommType Type() override { return CommType::THREADS; }
+  std::string group;
+  int rank, world_size, device;
 };
 
 // What the shuffle needs from a transport. All buffers are device memory; counts and offsets are in bytes.

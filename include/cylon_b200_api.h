@@ -24,6 +24,10 @@ typedef struct cylon_table cylon_table_t;     /* shared_ptr<cylon::Table> */
 int cylon_context_init(int32_t device, cylon_context_t **ctx);
 int cylon_nccl_unique_id(char id[128]); /* rank 0 creates, every rank passes the same bytes below */
 int cylon_context_init_distributed(int32_t rank, int32_t world_size, int32_t device, const char id[128], cylon_context_t **ctx);
+/* Ranks as host threads of one process (cylon::net::ThreadConfig): every thread calls this with the same group name and
+ * world size and its own rank, then uses its context from that thread only. For tests of the distributed operators on a
+ * box with fewer GPUs than ranks; no reference counterpart (the reference's ranks are MPI processes). */
+int cylon_context_init_threads(const char *group, int32_t rank, int32_t world_size, int32_t device, cylon_context_t **ctx);
 int cylon_context_set_stream(cylon_context_t *ctx, void *cuda_stream);
 /* CylonContext::AddConfig (ctx/cylon_context.hpp:85). Keys read by this library: "cylon.join.fused" ("0" = general hash
  * join only), "cylon.shuffle.peer" ("0" = NCCL send/recv instead of NVLink peer stores; must be the same on every rank),

@@ -1,0 +1,111 @@
+"""The multi-rank parity checks, shared by the NCCL worker (tests/dist_worker.py: one process per GPU) and the thread-rank
+worker (tests/thread_worker.py: ranks as threads on one GPU). Each rank runs the Distributed* operators and compares ITS
+result with the oracle's result for that rank (the oracle simulates all ranks) and, where the reference ships per-rank golden
+files, with those."""
+import json
+import os
+
+import numpy as np
+
+from oracle import pyoracle as orc
+from tests.helpers import assert_same_rows, from_orc, read_csv, synth_kv, to_orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+F64 = [np.int64, np.float64]
+
+
+def run_checks(api, ctx, rank, world):
+    checks = 0
+
+    # ---- reference golden files (cpp/test/join_test.cpp, set_op_test.cpp): per-rank expected outputs at world 2 and 4
+    if world in (2, 4):
+        l_all = [read_csv("csv1_%d.csv" % r, F64) for r in range(world)]
+        r_all = [read_csv("csv2_%d.csv" % r, F64) for r in range(world)]
+        L, R = from_orc(api, ctx, l_all[rank]), from_orc(api, ctx, r_all[rank])
+        for algo in ("sort", "hash"):
+            out = L.distributed_join(R, "inner", algo, [0], [0])
+            exp = read_csv("join_inner_%d_%d.csv" % (world, rank), [np.int64, np.float64, np.int64, np.float64])
+            assert_same_rows(to_orc(out), exp, "golden join_inner world %d rank %d %s" % (world, rank, algo))
+            checks += 1
+        for name in ("union", "subtract", "intersect"):
+            out = getattr(L, "distributed_" + name)(R)
+            assert_same_rows(to_orc(out), read_csv("%s_%d_%d.csv" % (name, world, rank), F64), "golden %s rank %d" % (name, rank))
+            checks += 1
+        ml, mr = read_csv("multi_join1.csv"), read_csv("multi_join2.csv")
+        out = from_orc(api, ctx, ml).distributed_join(from_orc(api, ctx, mr), "inner", "hash", [0, 1], [0, 1], "l_", "r_")
+        assert_same_rows(to_orc(out), read_csv("multi_join_%d_%d.csv" % (world, rank), [np.int64] * 6), "golden multi_join rank %d" % rank)
+        checks += 1
+    if world == 4:  # python/test/test_dist_rl.py:76-100
+        known = json.load(open(os.path.join(ROOT, "tests", "golden", "known_answers.json")))["test_dist_rl"]
+        t = from_orc(api, ctx, read_csv("user_usage_tm_%d.csv" % (rank + 1)))
+        assert t.distributed_join(t, "inner", "hash", [0], [0]).row_count == known["join_rows"][rank]
+        assert t.distributed_union(t).row_count == known["union_rows"][rank]
+        assert t.distributed_intersect(t).row_count == known["intersect_rows"][rank]
+        assert t.distributed_subtract(t).row_count == known["subtract_rows"][rank]
+        checks += 4
+
+    # ---- seeded synthetic tables against the oracle's simulation of every rank
+    def table(seed, r, n, strings, nulls):
+        k, v = synth_kv(n, 5000, seed, r)
+        cols = [orc.col(k, name="k"), orc.col(v, name="v"), orc.col((k % 7).astype(np.int32), name="i")]
+        if strings:
+            cols.append(orc.col([b"s%d" % (x % 23) for x in k], name="s"))
+        if nulls:
+            rng = np.random.default_rng(seed * 100 + r)
+            cols[1].validity = np.packbits(rng.random(n) < 0.9, bitorder="little")
+        return cols
+
+    for strings in (False, True):
+        lefts = [table(1, r, 20000 + 1000 * r, strings, False) for r in range(world)]
+        rights = [table(2, r, 15000 + 500 * r, strings, False) for r in range(world)]
+        L, R = from_orc(api, ctx, lefts[rank]), from_orc(api, ctx, rights[rank])
+        # Shuffle: rows conserved globally, and this rank holds exactly the oracle's partition
+        sh = L.shuffle([0])
+        assert_same_rows(to_orc(sh), orc.shuffle(lefts, [0])[rank], "shuffle rank %d" % rank)
+        for jt, ojt in (("inner", orc.INNER), ("left", orc.LEFT), ("right", orc.RIGHT), ("outer", orc.FULL_OUTER)):
+            for algo, oalgo, keys in (("hash", orc.HASH, [0]), ("sort", orc.SORT, [0, 2])):
+                out = L.distributed_join(R, jt, algo, keys, keys, "l_", "r_")
+                exp = orc.distributed_join(lefts, rights, keys, keys, ojt, oalgo, "l_", "r_")[rank]
+                assert_same_rows(to_orc(out), exp, "join %s %s rank %d" % (jt, algo, rank))
+                checks += 1
+        for name, op in (("union", orc.UNION), ("subtract", orc.SUBTRACT), ("intersect", orc.INTERSECT)):
+            # set ops need equal rows to exist: second table = first table of the next rank, re-seeded partly
+            rights2 = [lefts[(r + 1) % world] for r in range(world)]
+            out = getattr(L, "distributed_" + name)(from_orc(api, ctx, rights2[rank]))
+            assert_same_rows(to_orc(out), orc.distributed_set_op(lefts, rights2, op)[rank], "%s rank %d" % (name, rank))
+            checks += 1
+        out = L.distributed_unique([0, 2])
+        assert_same_rows(to_orc(out), orc.distributed_unique(lefts, [0, 2])[rank], "unique rank %d" % rank)
+        checks += 1
+
+    # nulls survive the shuffle (the reference drops them; compare against the inputs' own validity)
+    lefts = [table(3, r, 5000, True, True) for r in range(world)]
+    sh = to_orc(from_orc(api, ctx, lefts[rank]).shuffle([0]))
+    exp_parts = []
+    for src in range(world):
+        pid, _ = orc.hash_partition([lefts[src][0]], world)
+        idx = np.nonzero(pid == rank)[0]
+        part = [c.take(idx) for c in lefts[src]]
+        part[1].validity = np.packbits(lefts[src][1].valid_mask()[idx], bitorder="little")
+        exp_parts.append(part)
+    assert_same_rows(sh, orc.concat_tables(exp_parts), "shuffle with nulls rank %d" % rank)
+    checks += 1
+
+    # ---- group-by: SUM/MIN/MAX (pre-aggregated, doubled prefix) and with COUNT (raw rows shuffled)
+    tabs = [table(5, r, 30000, False, False) for r in range(world)]
+    T = from_orc(api, ctx, tabs[rank])
+    for ops, oops in ((["sum", "min", "max"], [orc.SUM, orc.MIN, orc.MAX]), (["sum", "count"], [orc.SUM, orc.COUNT])):
+        out = T.groupby([0], [1] * len(ops), ops, distributed=True)
+        exp = orc.distributed_hash_groupby(tabs, [0], [1] * len(ops), oops)[rank]
+        got = to_orc(out)
+        assert out.column_names == [c.name for c in exp], (out.column_names, [c.name for c in exp])
+        order_g, order_e = np.argsort(got[0].data, kind="stable"), np.argsort(exp[0].data, kind="stable")
+        assert np.array_equal(got[0].data[order_g], exp[0].data[order_e])
+        for g, e in zip(got[1:], exp[1:]):
+            if g.name.startswith("sum"):
+                assert np.allclose(g.data[order_g], e.data[order_e], rtol=1e-12, atol=0), g.name  # BASELINE.json tolerance
+            else:
+                assert np.array_equal(g.data[order_g], e.data[order_e]), g.name
+        checks += 1
+
+    return checks
