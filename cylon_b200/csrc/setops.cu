@@ -250,6 +250,10 @@ __global__ void offsets_to_lengths_kernel(const int32_t *__restrict__ off, int64
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) len[i] = off[i + 1] - off[i];
 }
 
+__global__ void gather_offsets_at_kernel(const int32_t *__restrict__ off, const int64_t *__restrict__ rows, int64_t n, int32_t *__restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = off[rows[i]];
+}
+
 __global__ void narrow_i64_i32_kernel(const int64_t *__restrict__ in, int64_t n1, int32_t *__restrict__ out) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n1; i += (int64_t)gridDim.x * blockDim.x) out[i] = (int32_t)in[i];
 }
@@ -288,6 +292,13 @@ int cyl_pack_validity(const uint8_t *bytes, int64_t n, uint8_t *bitmap, void *st
 int cyl_offsets_to_lengths(const int32_t *offsets, int64_t n, int32_t *lengths, void *stream) {
   if (n <= 0) return CYL_OK;
   offsets_to_lengths_kernel<<<grid1d(n), 256, 0, (cudaStream_t)stream>>>(offsets, n, lengths);
+  CYL_LAUNCH_CHECK();
+  return CYL_OK;
+}
+
+int cyl_gather_offsets_at(const int32_t *offsets, const int64_t *rows, int64_t n, int32_t *out, void *stream) {
+  if (n <= 0) return CYL_OK;
+  gather_offsets_at_kernel<<<grid1d(n), 256, 0, (cudaStream_t)stream>>>(offsets, rows, n, out);
   CYL_LAUNCH_CHECK();
   return CYL_OK;
 }

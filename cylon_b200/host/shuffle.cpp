@@ -33,6 +33,33 @@ struct Partitioned {
   std::vector<std::vector<int64_t>> byte_off; // per var-width column: [P+1] byte offsets at partition boundaries (else empty)
 };
 
+// byte_off[c][p] = offsets of variable-width column c at the first row of partition p (and at the end for p == P)
+Status BoundaryByteOffsets(const std::vector<std::shared_ptr<Column>> &cols, const int64_t *part_offsets_dev, uint32_t P, void *stream,
+                           std::vector<std::vector<int64_t>> *byte_off) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int nvar = 0;
+  for (const auto &c : cols) nvar += c->is_var_width() ? 1 : 0;
+  if (nvar == 0) return Status::OK();
+  DevBuf picked;
+  RETURN_CYLON_STATUS_IF_FAILED(picked.alloc((size_t)nvar * (P + 1) * 4, stream));
+  int v = 0;
+  for (const auto &c : cols) {
+    if (!c->is_var_width()) continue;
+    CYL_RETURN_IF_FAILED(cyl_gather_offsets_at(c->desc().offsets, part_offsets_dev, (int64_t)P + 1, picked.as<int32_t>() + (size_t)v * (P + 1), stream));
+    v++;
+  }
+  std::vector<int32_t> host((size_t)nvar * (P + 1), 0);
+  CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(host.data(), picked.p, host.size() * 4, cudaMemcpyDeviceToHost, s));
+  CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
+  v = 0;
+  for (size_t c = 0; c < cols.size(); c++) {
+    if (!cols[c]->is_var_width()) continue;
+    (*byte_off)[c].assign(host.begin() + (size_t)v * (P + 1), host.begin() + (size_t)(v + 1) * (P + 1));
+    v++;
+  }
+  return Status::OK();
+}
+
 // MapToHashPartitions + Split fused: returns the partition-ordered table and the partition boundaries (host)
 Status PartitionTable(const std::shared_ptr<Table> &table, const std::vector<int> &hash_cols, uint32_t P, Partitioned *out) {
   auto ctx = table->GetContext();
@@ -83,20 +110,28 @@ Status PartitionTable(const std::shared_ptr<Table> &table, const std::vector<int
   out->row_off.assign(P + 1, 0);
   CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(out->row_off.data(), part_offsets.p, (P + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
   CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
-  // byte offsets of variable-width columns at the partition boundaries
-  std::vector<int32_t> tmp(P + 1, 0);
-  for (int c = 0; c < ncols; c++) {
-    if (!out->cols[c]->is_var_width()) continue;
-    for (uint32_t p = 0; p <= P; p++)
-      CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(&tmp[p], out->cols[c]->desc().offsets + out->row_off[p], 4, cudaMemcpyDeviceToHost, s));
-    CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
-    out->byte_off[c].assign(tmp.begin(), tmp.end());
-  }
+  // byte offsets of variable-width columns at the partition boundaries: one small gather on the device and one copy per column
+  RETURN_CYLON_STATUS_IF_FAILED(BoundaryByteOffsets(out->cols, part_offsets.as<int64_t>(), P, stream, &out->byte_off));
   return Status::OK();
 }
 
 // zero-copy slice of rows [r0, r1) of a partition-ordered table (fixed width, byte-aligned validity only when r0 % 8 == 0)
-Status SliceRows(const Partitioned &pt, const std::shared_ptr<CylonContext> &ctx, uint32_t p, std::shared_ptr<Table> *out) {
+// one byte per row of every column that has a validity bitmap, made once and shared by all partitions' slices
+Status UnpackValidity(const Partitioned &pt, void *stream, std::vector<std::unique_ptr<DevBuf>> *bytes) {
+  bytes->clear();
+  for (const auto &src : pt.cols) {
+    bytes->emplace_back(nullptr);
+    const cyl_column_t &d = src->desc();
+    if (!d.validity) continue;
+    bytes->back().reset(new DevBuf());
+    RETURN_CYLON_STATUS_IF_FAILED(bytes->back()->alloc((size_t)src->length() + 1, stream));
+    CYL_RETURN_IF_FAILED(cyl_unpack_validity(d.validity, src->length(), bytes->back()->as<uint8_t>(), stream));
+  }
+  return Status::OK();
+}
+
+Status SliceRows(const Partitioned &pt, const std::vector<std::unique_ptr<DevBuf>> &validity_bytes, const std::shared_ptr<CylonContext> &ctx, uint32_t p,
+                 std::shared_ptr<Table> *out) {
   void *stream = ctx->GetStream();
   const int64_t r0 = pt.row_off[p], r1 = pt.row_off[p + 1], m = r1 - r0;
   std::vector<std::shared_ptr<Column>> cols;
@@ -114,13 +149,8 @@ Status SliceRows(const Partitioned &pt, const std::shared_ptr<CylonContext> &ctx
       RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate(src->name(), d.type, (int32_t)w, m, m * w, d.validity != nullptr, stream, &col));
       CYL_RETURN_IF_FAILED(cyl_memcpy_d2d(col->mutable_data(), static_cast<const char *>(d.data) + r0 * w, m * w, stream));
     }
-    if (d.validity) {
-      // re-align the bit range [r0, r1) to bit 0 through the byte form
-      DevBuf bytes;
-      RETURN_CYLON_STATUS_IF_FAILED(bytes.alloc((size_t)src->length() + 1, stream));
-      CYL_RETURN_IF_FAILED(cyl_unpack_validity(d.validity, src->length(), bytes.as<uint8_t>(), stream));
-      CYL_RETURN_IF_FAILED(cyl_pack_validity(bytes.as<uint8_t>() + r0, m, col->mutable_validity(), stream));
-    }
+    if (d.validity)  // re-align the bit range [r0, r1) to bit 0 through the byte form
+      CYL_RETURN_IF_FAILED(cyl_pack_validity(validity_bytes[c]->as<uint8_t>() + r0, m, col->mutable_validity(), stream));
     cols.push_back(col);
   }
   *out = std::make_shared<Table>(std::move(cols), ctx);
@@ -183,18 +213,13 @@ Status Split(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *ta
   pt.row_off.assign(P + 1, 0);
   CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(pt.row_off.data(), part_offsets.p, (P + 1) * 8, cudaMemcpyDeviceToHost, s));
   CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
-  std::vector<int32_t> tmp(P + 1, 0);
-  for (size_t c = 0; c < pt.cols.size(); c++) {
-    if (!pt.cols[c]->is_var_width()) continue;
-    for (uint32_t p = 0; p <= P; p++)
-      CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(&tmp[p], pt.cols[c]->desc().offsets + pt.row_off[p], 4, cudaMemcpyDeviceToHost, s));
-    CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
-    pt.byte_off[c].assign(tmp.begin(), tmp.end());
-  }
+  RETURN_CYLON_STATUS_IF_FAILED(BoundaryByteOffsets(pt.cols, part_offsets.as<int64_t>(), P, stream, &pt.byte_off));
   output.clear();
+  std::vector<std::unique_ptr<DevBuf>> vbytes;
+  RETURN_CYLON_STATUS_IF_FAILED(UnpackValidity(pt, stream, &vbytes));
   for (uint32_t p = 0; p < P; p++) {
     std::shared_ptr<Table> t;
-    RETURN_CYLON_STATUS_IF_FAILED(SliceRows(pt, ctx, p, &t));
+    RETURN_CYLON_STATUS_IF_FAILED(SliceRows(pt, vbytes, ctx, p, &t));
     output.push_back(t);
   }
   return Status::OK();
@@ -272,9 +297,11 @@ Status HashPartition(std::shared_ptr<Table> &table, const std::vector<int> &hash
   if (no_of_partitions < 1) return Status(Code::Invalid, "no_of_partitions must be positive");
   Partitioned pt;
   RETURN_CYLON_STATUS_IF_FAILED(PartitionTable(table, hash_columns, (uint32_t)no_of_partitions, &pt));
+  std::vector<std::unique_ptr<DevBuf>> vbytes;
+  RETURN_CYLON_STATUS_IF_FAILED(UnpackValidity(pt, table->GetContext()->GetStream(), &vbytes));
   for (int p = 0; p < no_of_partitions; p++) {
     std::shared_ptr<Table> t;
-    RETURN_CYLON_STATUS_IF_FAILED(SliceRows(pt, table->GetContext(), (uint32_t)p, &t));
+    RETURN_CYLON_STATUS_IF_FAILED(SliceRows(pt, vbytes, table->GetContext(), (uint32_t)p, &t));
     out->insert({p, t});
   }
   return Status::OK();

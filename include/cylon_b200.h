@@ -270,6 +270,10 @@ int cyl_concat_offsets(const int32_t *a_offsets, int64_t na, const int32_t *b_of
 int cyl_concat_validity(const uint8_t *va, int64_t na, const uint8_t *vb, int64_t nb, uint8_t *out, void *stream);
 /* validity bitmap <-> one byte per row (the shuffle moves validity as bytes because partition boundaries are not
  * byte aligned in a bitmap; arrow_all_to_all.cpp:97-107 ships the raw bitmap of already-split arrays). */
+/* out[i] = offsets[rows[i]] (device arrays): the byte offsets of a variable-width column at n chosen rows, e.g. at the
+ * partition boundaries, fetched with one kernel and one copy instead of one 4-byte copy each. Replaces the per-partition
+ * value_offset() reads of the string splitter (arrow/arrow_kernels.cpp:115-157). */
+int cyl_gather_offsets_at(const int32_t *offsets, const int64_t *rows, int64_t n, int32_t *out, void *stream);
 int cyl_unpack_validity(const uint8_t *bitmap /* NULL = all valid */, int64_t n, uint8_t *bytes, void *stream);
 int cyl_pack_validity(const uint8_t *bytes, int64_t n, uint8_t *bitmap, void *stream);
 /* int32 offsets <-> per-row lengths (the shuffle ships lengths and rebuilds offsets on the receiver).
