@@ -5,6 +5,8 @@
 #pragma once
 
 #include <cuda_runtime.h>
+
+#include <mutex>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -72,16 +74,28 @@ struct Scratch {
 };
 
 int num_sms();
-// "once per device" latch for per-(function, device) settings such as cudaFuncSetAttribute: first() is true the first
-// time it is asked with a given device current (a per-process flag would leave a second device of the process unset).
+// "once per device" latch for per-(function, device) settings such as cudaFuncSetAttribute (a per-process flag would leave
+// a second device of the process unset). Use as `if (auto once = latch.first()) { ...set... }`: the guard is true for the
+// thread that has to do the work and holds the latch's lock until the end of the if statement, so another host thread
+// (contexts may be driven from several threads) cannot launch between "marked done" and "attribute set".
 struct PerDeviceOnce {
   bool done[64] = {false};
-  bool first() {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
-    if (done[dev]) return false;
-    done[dev] = true;
-    return true;
+  std::mutex mu;
+  struct Guard {
+    PerDeviceOnce *latch;
+    int dev;
+    bool need;
+    explicit operator bool() const { return need; }
+    ~Guard() {
+      if (need && dev >= 0) latch->done[dev] = true;
+      latch->mu.unlock();
+    }
+  };
+  Guard first() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
+    mu.lock();
+    return Guard{this, dev, dev < 0 || !done[dev]};
   }
 };
 static inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -353,7 +353,7 @@ static size_t gb_smem_bytes(int naggs, int slots) {
 template <int W, int THREADS>
 static int launch_groupby_cfg(const GbArgs &a, int grid, cudaStream_t s) {
   static PerDeviceOnce attr_once;
-  if (attr_once.first()) CYL_CUDA(cudaFuncSetAttribute(groupby_fused8_kernel<W, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+  if (auto once_guard = attr_once.first()) CYL_CUDA(cudaFuncSetAttribute(groupby_fused8_kernel<W, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
   groupby_fused8_kernel<W, THREADS><<<grid, THREADS, gb_smem_bytes(a.naggs, a.slots), s>>>(a);
   CYL_LAUNCH_CHECK();
   return CYL_OK;

@@ -422,7 +422,7 @@ int cyl_hash_join_fused_inner(const cyl_column_t *lcols, int32_t nlcols, int32_t
   a.work_counter = reinterpret_cast<unsigned int *>(counters.as<char>() + 16);
 
   static PerDeviceOnce attr_once;
-  if (attr_once.first()) {
+  if (auto once_guard = attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused_join_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   }
   int64_t grid = (int64_t)num_sms() * 2;

@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(kBlkThreads) fused8_block_scatter_kernel(const
 template <int W>
 static int launch_block_scatter(const F8BlockArgs &a, size_t smem, cudaStream_t s) {
   static PerDeviceOnce attr_once;
-  if (attr_once.first()) {
+  if (auto once_guard = attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_block_scatter_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
   }
   fused8_block_scatter_kernel<W><<<(unsigned)a.nblocks, kBlkThreads, smem, s>>>(a);
@@ -404,7 +404,7 @@ static int f8_partition_blocks(const cyl_column_t *cols, int ncols, int key, int
   a.bin_total = totals.as<unsigned int>();
   const size_t smem = (size_t)nbins * sizeof(unsigned int);
   static PerDeviceOnce attr_once;
-  if (attr_once.first()) {
+  if (auto once_guard = attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
   }
   {
@@ -664,7 +664,7 @@ static size_t rs_smem_bytes() {
 template <int W, bool PASS_B>
 static int launch_radix_pass(const F8RadixArgs &a, int64_t tiles_bound, cudaStream_t s) {
   static PerDeviceOnce attr_once;
-  if (attr_once.first()) {
+  if (auto once_guard = attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_radix_pass_kernel<W, PASS_B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_smem_bytes<W>()));
   }
   int64_t grid = (int64_t)num_sms() * 2;
@@ -711,7 +711,7 @@ static int f8_bin_histogram(const F8PartArgs &a, int64_t nbins, int64_t tile_gue
     h.nblocks = div_up(a.n, tile);
     h.bin_total = a.hist;
     static PerDeviceOnce attr_once;
-    if (attr_once.first()) {
+    if (auto once_guard = attr_once.first()) {
       CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
     }
     ProfScope ps("fused_join_hist", s);
@@ -732,7 +732,7 @@ static int f8_bin_histogram(const F8PartArgs &a, int64_t nbins, int64_t tile_gue
     h.tile_rows = tile;
     h.nblocks = div_up(a.n, tile);
     static PerDeviceOnce attr_once2;
-    if (attr_once2.first()) {
+    if (auto once_guard2 = attr_once2.first()) {
       CYL_CUDA(cudaFuncSetAttribute(fused8_block_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kBlkMaxBins * 4)));
     }
     ProfScope ps("fused_join_hist", s);
@@ -859,7 +859,7 @@ int f8_partition(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_
 template <int BW, int PW>
 static int launch_join(const F8JoinArgs &a, int grid, size_t smem_bytes, cudaStream_t s) {
   static PerDeviceOnce attr_once;
-  if (attr_once.first()) {
+  if (auto once_guard = attr_once.first()) {
     CYL_CUDA(cudaFuncSetAttribute(fused8_join_kernel<BW, PW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   }
   fused8_join_kernel<BW, PW><<<grid, kF8Threads, smem_bytes, s>>>(a);

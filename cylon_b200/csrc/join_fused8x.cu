@@ -410,7 +410,7 @@ static int x_build_words(const cyl_column_t *cols, int ncols, const int32_t *key
 template <int BW, int PW>
 static int x_launch(const F8XArgs &a, int grid, size_t smem_bytes, cudaStream_t s) {
   static PerDeviceOnce attr_once;
-  if (attr_once.first()) CYL_CUDA(cudaFuncSetAttribute(fused8x_join_kernel<BW, PW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  if (auto once_guard = attr_once.first()) CYL_CUDA(cudaFuncSetAttribute(fused8x_join_kernel<BW, PW>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
   fused8x_join_kernel<BW, PW><<<grid, kXThreads, smem_bytes, s>>>(a);
   CYL_LAUNCH_CHECK();
   return CYL_OK;

@@ -507,8 +507,8 @@ static int grid_for(int64_t ntiles, int blocks_per_sm) {
 template <int MODE>
 static int launch_part(const PartArgs &a, size_t smem, cudaStream_t stream) {
   static PerDeviceOnce attr_once;  // the attribute belongs to the (function, device) pair
-  if (smem > 48 * 1024 && attr_once.first()) {
-    CYL_CUDA(cudaFuncSetAttribute(partition_tiles_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+  if (smem > 48 * 1024) {
+    if (auto once_guard = attr_once.first()) CYL_CUDA(cudaFuncSetAttribute(partition_tiles_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
   }
   const int bps = smem > 16 * 1024 ? 2 : 8;
   partition_tiles_kernel<MODE><<<grid_for(a.ntiles, bps), kPartThreads, smem, stream>>>(a);
@@ -933,7 +933,7 @@ int cyl_partition_plan_scatter(cyl_partition_plan_t *plan, void *const *dst, con
     sa.warp_bytes = (2 * kStageMaxP + 4) * (int)sizeof(uint32_t) + off;
     const size_t smem = (size_t)sa.warp_bytes * kPartWarps;
     static PerDeviceOnce attr_once;
-    if (attr_once.first()) {
+    if (auto once_guard = attr_once.first()) {
       CYL_CUDA(cudaFuncSetAttribute(partition_stage_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
     }
     bool all8 = sa.bulk && plan->ncols <= 3 && a.rounds == 16;
