@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("world,peer", [(2, "1"), (2, "0"), (3, "1"), (4, "1"), (4, "0")])
+@pytest.mark.parametrize("world,peer", [(2, "1"), (3, "0"), (4, "1")])
 def test_distributed_operators_with_thread_ranks(world, peer):
     p = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "thread_worker.py"), str(world), peer], capture_output=True, text=True,
                        timeout=900, cwd=ROOT)
