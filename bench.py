@@ -161,9 +161,14 @@ class Env:
             if self.rank == 0:
                 idt = torch.frombuffer(bytearray(api.nccl_unique_id()), dtype=torch.uint8).cuda()
             self.dist.broadcast(idt, 0)
-            return api.CylonContext(device=self.local_rank, distributed=True, rank=self.rank, world_size=self.world,
-                                    nccl_id=idt.cpu().numpy().tobytes())
-        return api.CylonContext(device=self.local_rank)
+            ctx = api.CylonContext(device=self.local_rank, distributed=True, rank=self.rank, world_size=self.world,
+                                   nccl_id=idt.cpu().numpy().tobytes())
+        else:
+            ctx = api.CylonContext(device=self.local_rank)
+        for kv in filter(None, os.environ.get("CYLON_CONFIG", "").split(";")):  # A/B runs: CYLON_CONFIG="cylon.join.overlap=0"
+            k, v = kv.split("=", 1)
+            ctx.add_config(k, v)
+        return ctx
 
     def barrier(self):
         self.torch.cuda.synchronize()

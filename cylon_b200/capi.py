@@ -419,3 +419,37 @@ def hash_join_fused(lcols, lkey, rcols, rkey, capacity=None, stream=None):
             cols = [DCol(c.type, m.value, o, byte_width=c.byte_width, name=c.name) for c, o in zip(list(lcols) + list(rcols), outs)]
             return cols, m.value, attempts
         capacity = m.value
+
+
+def hash_join_fused_two_step(lcols, lkey, rcols, rkey, capacity=None, stream=None, right_stream=None):
+    """cyl_hash_join_fused_partition (each table, possibly on its own stream) + cyl_hash_join_fused_probe
+    -> (list of DCol output columns, rows, attempts). The caller orders the two streams."""
+    L = lib()
+    L.cyl_hash_join_fused_side_free.restype = None
+    nl, nr = lcols[0].length, rcols[0].length
+    if capacity is None:
+        capacity = max(nl, nr) + max(nl, nr) // 8 + 1024
+    ls, rs = C.c_void_p(), C.c_void_p()
+    try:
+        check(L.cyl_hash_join_fused_partition(c_columns(lcols), len(lcols), C.c_int32(lkey), C.c_int64(nl), None, C.c_int64(nl), C.byref(ls),
+                                              C.c_void_p(stream)))
+        check(L.cyl_hash_join_fused_partition(c_columns(rcols), len(rcols), C.c_int32(rkey), C.c_int64(nr), ls, C.c_int64(0), C.byref(rs),
+                                              C.c_void_p(right_stream if right_stream is not None else stream)))
+        if right_stream is not None:
+            sync(right_stream)
+        attempts = 0
+        while True:
+            attempts += 1
+            outs = [DeviceBuffer(max(1, capacity * 8)) for _ in list(lcols) + list(rcols)]
+            ptrs = (C.c_void_p * len(outs))(*[o.ptr for o in outs])
+            m = C.c_int64()
+            check(L.cyl_hash_join_fused_probe(ls, rs, C.c_int64(capacity), ptrs, C.byref(m), C.c_void_p(stream)))
+            if m.value <= capacity:
+                cols = [DCol(c.type, m.value, o, byte_width=8, name=c.name) for c, o in zip(list(lcols) + list(rcols), outs)]
+                return cols, m.value, attempts
+            capacity = m.value
+    finally:
+        sync(stream)
+        L.cyl_hash_join_fused_side_free(ls)
+        L.cyl_hash_join_fused_side_free(rs)
+

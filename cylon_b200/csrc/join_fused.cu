@@ -19,6 +19,8 @@
 // kernel always returns the exact row count and the caller repeats the call with a larger capacity if it did not fit.
 // Bins larger than the shared-memory budget (key skew) are processed in several build chunks, which is exact for an
 // inner join. Output order is unspecified (row multiset == reference).
+#include <memory>
+
 #include "common.cuh"
 #include "join_fused.cuh"
 #include "scan.cuh"
@@ -325,6 +327,48 @@ int cyl_hash_join_fused_supported(const cyl_column_t *lcols, int32_t nlcols, int
   if (lcols[lkey].type != rcols[rkey].type) return 0;
   FusedPlan pl;
   return plan_smem(lcols, nlcols, &pl) && plan_smem(rcols, nrcols, &pl) ? 1 : 0;
+}
+
+// ---- the all-8-byte fused join in two steps (see include/cylon_b200.h) ----
+struct cyl_join_side {
+  F8Partitioned *p = nullptr;
+  int ncols = 0;
+};
+
+int cyl_hash_join_fused_partition(const cyl_column_t *cols, int32_t ncols, int32_t key, int64_t nrows, const cyl_join_side_t *like, int64_t build_rows_hint,
+                                  cyl_join_side_t **side, void *stream) {
+  if (!side) return fail(CYL_Invalid, "cyl_hash_join_fused_partition: null output");
+  *side = nullptr;
+  if (ncols < 1 || ncols > kFused8MaxCols || key < 0 || key >= ncols) return fail(CYL_Invalid, "cyl_hash_join_fused_partition: bad column / key count");
+  for (int c = 0; c < ncols; c++)
+    if (cols[c].byte_width != 8 || cols[c].length != nrows) return fail(CYL_Invalid, "cyl_hash_join_fused_partition: column %d is not an 8-byte column of %lld rows", c, (long long)nrows);
+  if (nrows < 0 || nrows > 0xFFFFFFFEll) return fail(CYL_CapacityError, "cyl_hash_join_fused_partition: row count out of range");
+  int64_t nbins;
+  int shift;
+  if (like) {
+    nbins = fused8_side_bins(like->p);
+    shift = fused8_side_shift(like->p);
+  } else {
+    fused8_bins_for(ncols, build_rows_hint > nrows ? build_rows_hint : nrows, &nbins, &shift);
+  }
+  std::unique_ptr<cyl_join_side> out(new cyl_join_side());
+  out->ncols = ncols;
+  CYL_TRY(fused8_partition_side(cols, ncols, key, nrows, nbins, shift, &out->p, (cudaStream_t)stream));
+  *side = out.release();
+  return CYL_OK;
+}
+
+int cyl_hash_join_fused_probe(const cyl_join_side_t *left, const cyl_join_side_t *right, int64_t capacity, void *const *out_cols, int64_t *num_rows,
+                              void *stream) {
+  if (!left || !right || !num_rows) return fail(CYL_Invalid, "cyl_hash_join_fused_probe: null argument");
+  // build side = the table that was partitioned first decides nothing here: either works; take the left (ties -> left, hash_join.cpp:226-231)
+  return fused8_probe(left->p, right->p, out_cols, out_cols + left->ncols, capacity, num_rows, (cudaStream_t)stream);
+}
+
+void cyl_hash_join_fused_side_free(cyl_join_side_t *side) {
+  if (!side) return;
+  fused8_side_free(side->p);
+  delete side;
 }
 
 int cyl_tune_set(int32_t key, int32_t value) {

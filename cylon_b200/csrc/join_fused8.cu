@@ -10,6 +10,8 @@
 //     contiguous), probed 4 rows per thread per tile so the block scan, the barrier pair and the single global
 //     atomicAdd that reserves output rows are paid once per 2048 probe rows, and everything is compile-time sized
 //     (no per-value width switches).
+#include <memory>
+
 #include "common.cuh"
 #include "join_fused.cuh"
 #include "scan.cuh"
@@ -886,8 +888,9 @@ bool fused8_eligible(const cyl_column_t *lcols, int nlcols, const cyl_column_t *
   return true;
 }
 
-int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const cyl_column_t *pcols, int npc, int pkey, int64_t np,
-                void *const *bout, void *const *pout, int64_t capacity, int64_t *num_rows, cudaStream_t s) {
+// Shared-memory plan of the join kernel for a build side of `nbc` words: rows per bin, chain heads, bytes; and the bin count
+// for `nb` build rows.
+static void f8_plan(int nbc, int64_t nb, int *cap_out, int *nheads_out, size_t *smem_out, int64_t *nbins_out, int *shift_out) {
   // shared memory per CTA: records + 16-bit next links + 32-bit heads (2 CTAs per SM)
   const size_t budget = 104 * 1024;
   int cap = 16384, nheads = 0;  // next links are 16-bit and 0xFFFF ends a chain
@@ -903,28 +906,66 @@ int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const 
   if (g_force_bins_log2 > 0) nbins = 1ll << g_force_bins_log2;  // test hook: more (smaller) bins than the size asks for
   int bits = 0;
   while ((1ll << bits) < nbins) bits++;
-  const int shift = 64 - bits;
+  *cap_out = cap;
+  *nheads_out = nheads;
+  *smem_out = smem_bytes;
+  *nbins_out = nbins;
+  *shift_out = 64 - bits;
+}
 
-  Scratch brec, prec, boff, poff, counters;
-  CYL_TRY(brec.alloc((size_t)nb * nbc * 8 + 16, s));
-  CYL_TRY(prec.alloc((size_t)np * npc * 8 + 16, s));
-  CYL_TRY(boff.alloc((size_t)(nbins + 1) * sizeof(int64_t), s));
-  CYL_TRY(poff.alloc((size_t)(nbins + 1) * sizeof(int64_t), s));
-  CYL_TRY(f8_partition(bcols, nbc, bkey, nb, nbins, shift, brec.as<uint64_t>(), boff.as<int64_t>(), s));
-  CYL_TRY(f8_partition(pcols, npc, pkey, np, nbins, shift, prec.as<uint64_t>(), poff.as<int64_t>(), s));
+// One table radix-partitioned into the join's bins: the unit the distributed join prepares for the first table while the
+// second one is still being shuffled (host/shuffle.cpp).
+struct F8Partitioned {
+  Scratch rec, off;
+  int64_t n = 0, nbins = 0;
+  int ncols = 0, key = 0, shift = 0, key_is_f64 = 0;
+};
 
+int fused8_partition_side(const cyl_column_t *cols, int ncols, int key, int64_t n, int64_t nbins, int shift, F8Partitioned **out, cudaStream_t s) {
+  std::unique_ptr<F8Partitioned> p(new F8Partitioned());
+  p->n = n;
+  p->nbins = nbins;
+  p->ncols = ncols;
+  p->key = key;
+  p->shift = shift;
+  p->key_is_f64 = cols[key].type == CYL_DOUBLE;
+  CYL_TRY(p->rec.alloc((size_t)n * ncols * 8 + 16, s));
+  CYL_TRY(p->off.alloc((size_t)(nbins + 1) * sizeof(int64_t), s));
+  CYL_TRY(f8_partition(cols, ncols, key, n, nbins, shift, p->rec.as<uint64_t>(), p->off.as<int64_t>(), s));
+  *out = p.release();
+  return CYL_OK;
+}
+
+void fused8_side_free(F8Partitioned *p) { delete p; }
+int64_t fused8_side_bins(const F8Partitioned *p) { return p->nbins; }
+int fused8_side_shift(const F8Partitioned *p) { return p->shift; }
+void fused8_bins_for(int build_words, int64_t build_rows, int64_t *nbins, int *shift) {
+  int cap, nheads;
+  size_t smem;
+  f8_plan(build_words, build_rows, &cap, &nheads, &smem, nbins, shift);
+}
+
+int fused8_probe(const F8Partitioned *b, const F8Partitioned *p, void *const *bout, void *const *pout, int64_t capacity, int64_t *num_rows,
+                 cudaStream_t s) {
+  if (b->nbins != p->nbins || b->shift != p->shift) return fail(CYL_Invalid, "fused join: the two sides were partitioned into different bins");
+  int cap, nheads, shift;
+  size_t smem_bytes;
+  int64_t nbins_unused;
+  f8_plan(b->ncols, b->n, &cap, &nheads, &smem_bytes, &nbins_unused, &shift);  // cap depends on the record width only
+  const int nbc = b->ncols, npc = p->ncols;
+  Scratch counters;
   F8JoinArgs a;
   memset(&a, 0, sizeof(a));
-  a.brec = brec.as<uint64_t>();
-  a.prec = prec.as<uint64_t>();
-  a.b_off = boff.as<int64_t>();
-  a.p_off = poff.as<int64_t>();
+  a.brec = b->rec.as<uint64_t>();
+  a.prec = p->rec.as<uint64_t>();
+  a.b_off = b->off.as<int64_t>();
+  a.p_off = p->off.as<int64_t>();
   for (int c = 0; c < nbc; c++) a.bout[c] = static_cast<uint64_t *>(bout[c]);
   for (int c = 0; c < npc; c++) a.pout[c] = static_cast<uint64_t *>(pout[c]);
-  a.nbins = nbins;
-  a.bkey = bkey;
-  a.pkey = pkey;
-  a.key_is_f64 = bcols[bkey].type == CYL_DOUBLE;
+  a.nbins = b->nbins;
+  a.bkey = b->key;
+  a.pkey = p->key;
+  a.key_is_f64 = b->key_is_f64;
   a.cap_rows = cap;
   a.nheads = nheads;
   a.capacity = capacity;
@@ -933,7 +974,7 @@ int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const 
   a.out_cursor = counters.as<unsigned long long>();
   a.work_counter = reinterpret_cast<unsigned int *>(counters.as<char>() + 16);
   int64_t grid = (int64_t)num_sms() * 2;
-  if (grid > nbins) grid = nbins;
+  if (grid > a.nbins) grid = a.nbins;
   {
     ProfScope ps("fused_join_probe", s);
     int rc;
@@ -950,6 +991,19 @@ int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const 
   CYL_CUDA(cudaStreamSynchronize(s));
   *num_rows = (int64_t)m;
   return CYL_OK;
+}
+
+int fused8_join(const cyl_column_t *bcols, int nbc, int bkey, int64_t nb, const cyl_column_t *pcols, int npc, int pkey, int64_t np,
+                void *const *bout, void *const *pout, int64_t capacity, int64_t *num_rows, cudaStream_t s) {
+  int64_t nbins;
+  int shift;
+  fused8_bins_for(nbc, nb, &nbins, &shift);
+  F8Partitioned *b = nullptr, *p = nullptr;
+  CYL_TRY(fused8_partition_side(bcols, nbc, bkey, nb, nbins, shift, &b, s));
+  std::unique_ptr<F8Partitioned> bguard(b);
+  CYL_TRY(fused8_partition_side(pcols, npc, pkey, np, nbins, shift, &p, s));
+  std::unique_ptr<F8Partitioned> pguard(p);
+  return fused8_probe(b, p, bout, pout, capacity, num_rows, s);
 }
 
 }  // namespace cylb

@@ -425,6 +425,22 @@ std::shared_ptr<CylonContext> CylonContext::InitDistributed(const std::shared_pt
 
 void CylonContext::Finalize() {
   if (communicator) communicator->Finalize();
+  if (aux_stream) {
+    cudaStreamDestroy(static_cast<cudaStream_t>(aux_stream));
+    aux_stream = nullptr;
+  }
+}
+
+void *CylonContext::GetAuxStream() {
+  if (!aux_stream) {
+    cudaStream_t s = nullptr;
+    if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    aux_stream = s;
+  }
+  return aux_stream;
 }
 
 std::vector<int> CylonContext::GetNeighbours(bool include_self) {

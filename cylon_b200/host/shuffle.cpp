@@ -17,6 +17,8 @@
 //  * received chunks are ordered by source rank (the reference orders by arrival: non-deterministic).
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 #include "cylon/partition/partition.hpp"
 #include "cylon/table.hpp"
 #include "table_ops.hpp"
@@ -576,6 +578,90 @@ static Status ShuffleTwo(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Tab
   return ShuffleByHashing(ctx, right, rcols, rout);
 }
 
+// INNER join of all-8-byte tables on one key (the benchmark shape): the left table is shuffled first and radix-partitioned
+// into the join's bins on the context's SECOND stream while the right table is still being shuffled on the first -- its
+// histogram and the host round trips of its count exchange leave the GPU idle otherwise, and the NVLink-bound scatter and
+// the HBM-bound partition passes want different resources. The reference runs the two shuffles and the join strictly one
+// after the other (table.cpp:159-179,482-502). *done == false: the shape does not qualify, nothing was touched.
+static Status OverlappedInnerJoin(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &left, std::shared_ptr<Table> &right,
+                                  const join::config::JoinConfig &cfg, std::shared_ptr<Table> &out, bool *done) {
+  *done = false;
+  const auto &lidx = cfg.GetLeftColumnIdx(), &ridx = cfg.GetRightColumnIdx();
+  if (cfg.GetType() != join::config::INNER || lidx.size() != 1 || ridx.size() != 1) return Status::OK();
+  if (ctx->GetConfig("cylon.join.fused", "1") == "0" || ctx->GetConfig("cylon.join.overlap", "1") == "0") return Status::OK();
+  {
+    const auto la = detail::AllDescs(*left), ra = detail::AllDescs(*right);
+    if (!cyl_hash_join_fused_supported(la.data(), (int32_t)la.size(), lidx[0], ra.data(), (int32_t)ra.size(), ridx[0], CYL_JOIN_INNER)) return Status::OK();
+    for (const auto &t : {left, right})  // the two-step entry points take the all-8-byte shape only
+      for (const auto &c : t->GetColumns())
+        if (c->byte_width() != 8) return Status::OK();
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(ctx->GetStream());
+  cudaStream_t aux = static_cast<cudaStream_t>(ctx->GetAuxStream());
+  if (!aux) return Status::OK();
+  *done = true;
+
+  struct Events {
+    cudaEvent_t e[3] = {nullptr, nullptr, nullptr};
+    ~Events() {
+      for (auto ev : e)
+        if (ev) cudaEventDestroy(ev);
+    }
+  } ev;
+  for (auto &e : ev.e) CUDA_RETURN_IF_FAILED(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  struct Sides {
+    cyl_join_side_t *l = nullptr, *r = nullptr;
+    ~Sides() {
+      cyl_hash_join_fused_side_free(l);
+      cyl_hash_join_fused_side_free(r);
+    }
+  } sides;
+
+  std::shared_ptr<Table> l, r;
+  const std::string lprefix = cfg.GetLeftTableSuffix(), rprefix = cfg.GetRightTableSuffix();
+  RETURN_CYLON_STATUS_IF_FAILED(ShuffleByHashing(ctx, left, lidx, l));
+  CUDA_RETURN_IF_FAILED(cudaEventRecord(ev.e[0], s));
+  CUDA_RETURN_IF_FAILED(cudaStreamWaitEvent(aux, ev.e[0], 0));
+  const auto lall = detail::AllDescs(*l);
+  CYL_RETURN_IF_FAILED(cyl_hash_join_fused_partition(lall.data(), (int32_t)lall.size(), lidx[0], l->Rows(), nullptr, l->Rows(), &sides.l, aux));
+  CUDA_RETURN_IF_FAILED(cudaEventRecord(ev.e[1], aux));
+  RETURN_CYLON_STATUS_IF_FAILED(ShuffleByHashing(ctx, right, ridx, r));
+  const auto rall = detail::AllDescs(*r);
+  CYL_RETURN_IF_FAILED(cyl_hash_join_fused_partition(rall.data(), (int32_t)rall.size(), ridx[0], r->Rows(), sides.l, 0, &sides.r, s));
+  CUDA_RETURN_IF_FAILED(cudaStreamWaitEvent(s, ev.e[1], 0));
+
+  const int64_t nl = l->Rows(), nr = r->Rows();
+  int64_t capacity = std::max(nl, nr) + std::max(nl, nr) / 8 + 1024;
+  Status result(Code::ExecutionError, "fused join did not fit its exact capacity");
+  for (int attempt = 0; attempt < 2; attempt++) {
+    std::vector<std::shared_ptr<Column>> cols;
+    std::vector<void *> outs;
+    for (int side = 0; side < 2; side++) {
+      const Table &t = side == 0 ? *l : *r;
+      for (const auto &src : t.GetColumns()) {
+        std::shared_ptr<Column> col;
+        RETURN_CYLON_STATUS_IF_FAILED(Column::Allocate((side == 0 ? lprefix : rprefix) + src->name(), src->type(), 8, capacity, capacity * 8, false,
+                                                       ctx->GetStream(), &col));
+        outs.push_back(col->mutable_data());
+        cols.push_back(col);
+      }
+    }
+    int64_t m = 0;
+    CYL_RETURN_IF_FAILED(cyl_hash_join_fused_probe(sides.l, sides.r, capacity, outs.data(), &m, ctx->GetStream()));
+    if (m <= capacity) {
+      for (auto &c : cols) c->truncate(m);
+      out = std::make_shared<Table>(std::move(cols), ctx);
+      result = Status::OK();
+      break;
+    }
+    capacity = m;
+  }
+  // the left side's scratch goes back to the second stream's free lists: later work there must come after this probe
+  CUDA_RETURN_IF_FAILED(cudaEventRecord(ev.e[2], s));
+  CUDA_RETURN_IF_FAILED(cudaStreamWaitEvent(aux, ev.e[2], 0));
+  return result;
+}
+
 Status DistributedJoin(std::shared_ptr<Table> &left, std::shared_ptr<Table> &right, const join::config::JoinConfig &cfg,
                        std::shared_ptr<Table> &out) {
   if (left == nullptr) return Status(Code::KeyError, "Couldn't find the left table");
@@ -586,6 +672,11 @@ Status DistributedJoin(std::shared_ptr<Table> &left, std::shared_ptr<Table> &rig
   RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(*right, cfg.GetRightColumnIdx(), "DistributedJoin(right)"));
   std::shared_ptr<Table> l, r;
   detail::StageTrace trace("DistributedJoin", ctx->GetStream());
+  {
+    bool done = false;
+    RETURN_CYLON_STATUS_IF_FAILED(OverlappedInnerJoin(ctx, left, right, cfg, out, &done));
+    if (done) return Status::OK();
+  }
   RETURN_CYLON_STATUS_IF_FAILED(ShuffleTwo(ctx, left, cfg.GetLeftColumnIdx(), right, cfg.GetRightColumnIdx(), l, r));
   trace.mark("shuffle both tables");
   Status st = Join(l, r, cfg, out);

@@ -45,6 +45,7 @@ class CylonContext {
   int GetDevice() const { return device; }
   void *GetStream() const { return stream; }   // cudaStream_t
   void SetStream(void *s) { stream = s; }      // caller-owned stream (e.g. torch's current stream)
+  void *GetAuxStream();                        // second (non-blocking) stream of this context, created on first use; nullptr on failure
 
  private:
   std::unordered_map<std::string, std::string> config{};
@@ -53,6 +54,7 @@ class CylonContext {
   int32_t sequence_no = 0;
   int device = 0;
   void *stream = nullptr;
+  void *aux_stream = nullptr;
 };
 
 }  // namespace cylon

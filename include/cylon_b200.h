@@ -172,6 +172,17 @@ int cyl_hash_join_fused_supported(const cyl_column_t *lcols /* host array */, in
 int cyl_hash_join_fused_inner(const cyl_column_t *lcols /* host array */, int32_t nlcols, int32_t lkey, const cyl_column_t *rcols /* host array */,
                               int32_t nrcols, int32_t rkey, int64_t nl, int64_t nr, int64_t capacity, void *const *out_cols /* host array */,
                               int64_t *num_rows /* host out */, void *stream);
+/* The INNER fused join of all-8-byte tables in two steps: partition each table into the join's bins (any stream), then probe.
+ * A distributed join partitions the table that has arrived while the other one is still being shuffled. `like` (may be NULL)
+ * makes the second table use the first one's bins; without it the bins are sized for max(nrows, build_rows_hint) build rows.
+ * The probe treats `left` as the build side; out_cols / capacity / num_rows as in cyl_hash_join_fused_inner. A side may be
+ * probed more than once (capacity retry) and must be freed. Same reference code replaced as cyl_hash_join_fused_inner. */
+typedef struct cyl_join_side cyl_join_side_t;
+int cyl_hash_join_fused_partition(const cyl_column_t *cols /* host array */, int32_t ncols, int32_t key, int64_t nrows, const cyl_join_side_t *like,
+                                  int64_t build_rows_hint, cyl_join_side_t **side /* host out */, void *stream);
+int cyl_hash_join_fused_probe(const cyl_join_side_t *left, const cyl_join_side_t *right, int64_t capacity, void *const *out_cols /* host array */,
+                              int64_t *num_rows /* host out */, void *stream);
+void cyl_hash_join_fused_side_free(cyl_join_side_t *side);
 /* The same engine for LEFT / RIGHT / FULL_OUTER joins, keys of one or two columns and tables that mix 4- and 8-byte
  * numeric / temporal columns (at most 4 record words per side; a two-column key uses one of them). out_cols: nlcols +
  * nrcols device buffers of `capacity` values of each column's width, left columns first. left_valid / right_valid: device

@@ -181,3 +181,21 @@ def test_fused_join_forced_bin_counts(cy, bits):
     finally:
         cy.check(cy.lib().cyl_hash_join_fused_set_bins_log2(0))
     assert cy.lib().cyl_hash_join_fused_set_bins_log2(19) != 0
+
+
+@pytest.mark.parametrize("nl,nr,dom,second_stream", [(0, 5, 3, False), (1000, 700, 300, False), (300007, 250003, 200000, True), (4000, 4000, 7, True)])
+def test_fused_join_two_step_matches_one_call(cy, nl, nr, dom, second_stream):
+    """cyl_hash_join_fused_partition + _probe (what DistributedJoin overlaps with the second shuffle): the same row
+    multiset as the oracle, also with the right table partitioned on another stream and with a capacity retry (dom=7)."""
+    import torch
+    rng = np.random.default_rng(nl * 3 + nr)
+    l = [orc.col(rng.integers(0, dom, nl).astype(np.int64)), orc.col(rng.random(nl)), orc.col(rng.integers(0, 2 ** 50, nl).astype(np.uint64))]
+    r = [orc.col(rng.random(nr)), orc.col(rng.integers(0, dom, nr).astype(np.int64))]
+    other = torch.cuda.Stream() if second_stream else None
+    cols, m, attempts = cy.hash_join_fused_two_step(_to_dev(cy, l), 0, _to_dev(cy, r), 1, right_stream=other.cuda_stream if other else None)
+    exp = orc.join(l, r, [0], [1], orc.INNER, orc.HASH)
+    assert m == exp[0].length
+    assert_same_rows(_out_table(cy, cols), exp)
+    if dom == 7:
+        assert attempts == 2
+
