@@ -19,6 +19,7 @@ the seeded generator, and a smaller run of the same operator, rank by rank, agai
 oracle/_ref (else the oracle). A mismatch makes the run exit non-zero.
 """
 import argparse
+import faulthandler
 import json
 import os
 import subprocess
@@ -27,6 +28,11 @@ import threading
 import time
 
 import numpy as np
+
+# Streams share the device's hardware work queues (8 by default). The e2e arm keeps several steps in flight, each with its
+# own stream, second stream and NCCL communicator; two streams aliased onto one queue would order one communicator's
+# collective behind another's. Must be set before the CUDA context exists.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -840,6 +846,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     args = ap.parse_args()
+    # a stalled run (a rank that died, a collective left waiting) prints every thread's stack and exits instead of hanging
+    faulthandler.dump_traceback_later(int(os.environ.get("BENCH_WATCHDOG_S", "1500")), exit=True)
     if args.impl == "reference":
         return run_reference(args)
 
