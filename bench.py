@@ -914,9 +914,31 @@ def main():
 
         d2h_bytes = [0]
 
-        def e2e_step(cx, outs):
+        turn = {"next": 0, "failed": False}
+        turn_cv = threading.Condition()
+
+        def e2e_step(cx, outs, step_no=None):
             tabs = wl.upload(cx, host)
-            out = wl.run(tabs)
+            # The operators of the steps in flight run one at a time, in step order, on every rank: each lane has its own
+            # communicator, and two ranks that entered different lanes' collectives first would wait for each other for
+            # good. Uploads and downloads of the neighbouring steps are what overlaps with an operator.
+            if step_no is not None:
+                with turn_cv:
+                    turn_cv.wait_for(lambda: turn["next"] == step_no or turn["failed"])
+                    if turn["failed"]:
+                        raise RuntimeError("another lane failed")
+            try:
+                out = wl.run(tabs)
+            except BaseException:
+                with turn_cv:
+                    turn["failed"] = True
+                    turn_cv.notify_all()
+                raise
+            if step_no is not None:
+                capi.sync(cx._stream)  # this lane's last collective has run before the next lane issues its first
+                with turn_cv:
+                    turn["next"] = step_no + 1
+                    turn_cv.notify_all()
             mm = out.row_count
             d2h_bytes[0] = download_result(out, outs)
             out.free()
@@ -929,7 +951,7 @@ def main():
         # own stream and its own pinned result buffers, take alternate steps, so one step's result download (PCIe up)
         # overlaps the next step's input upload (PCIe down) and the operator of a third. Every step still uploads all of
         # its inputs and downloads its whole result inside the timed region. Lane i of every rank runs the same sequence
-        # of steps on communicator i, so the collectives of one lane never wait for another lane's.
+        # of steps on communicator i.
         nlanes = max(1, min(args.e2e_lanes, args.steps))
         if args.config == "shuffle" and world == 1:
             nlanes = 1  # wl.state["parts"] is per process
@@ -950,9 +972,12 @@ def main():
             try:
                 torch.cuda.set_device(env.local_rank)  # the CUDA current device is per host thread
                 for _s in range(li, args.steps, len(lanes)):
-                    e2e_step(*lanes[li])
+                    e2e_step(*lanes[li], step_no=_s)
             except BaseException as exc:  # a failed lane must fail the run, not vanish with its thread
                 errors.append(exc)
+                with turn_cv:
+                    turn["failed"] = True
+                    turn_cv.notify_all()
 
         if len(lanes) == 1:
             lane_main(0)

@@ -22,11 +22,13 @@ def run_checks(api, ctx, rank, world):
         l_all = [read_csv("csv1_%d.csv" % r, F64) for r in range(world)]
         r_all = [read_csv("csv2_%d.csv" % r, F64) for r in range(world)]
         L, R = from_orc(api, ctx, l_all[rank]), from_orc(api, ctx, r_all[rank])
-        for algo in ("sort", "hash"):
+        for algo, overlap in (("sort", "0"), ("hash", "0"), ("hash", "1")):  # "1": left side partitioned on a second stream during the right shuffle
+            ctx.add_config("cylon.join.overlap", overlap)
             out = L.distributed_join(R, "inner", algo, [0], [0])
             exp = read_csv("join_inner_%d_%d.csv" % (world, rank), [np.int64, np.float64, np.int64, np.float64])
-            assert_same_rows(to_orc(out), exp, "golden join_inner world %d rank %d %s" % (world, rank, algo))
+            assert_same_rows(to_orc(out), exp, "golden join_inner world %d rank %d %s overlap %s" % (world, rank, algo, overlap))
             checks += 1
+        ctx.add_config("cylon.join.overlap", "0")
         for name in ("union", "subtract", "intersect"):
             out = getattr(L, "distributed_" + name)(R)
             assert_same_rows(to_orc(out), read_csv("%s_%d_%d.csv" % (name, world, rank), F64), "golden %s rank %d" % (name, rank))
