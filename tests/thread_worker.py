@@ -10,20 +10,21 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from cylon_b200 import api  # noqa: E402
-from tests.dist_checks import run_checks  # noqa: E402
+from tests.dist_checks import SharedExpectations, run_checks  # noqa: E402
 
 
 def main():
     world = int(sys.argv[1])
     peer = sys.argv[2] if len(sys.argv) > 2 else "1"
     results, errors = [0] * world, []
+    shared = SharedExpectations()
 
     def rank_main(rank):
         try:
             ctx = api.CylonContext(device=0, thread_group="ranks-%d" % os.getpid(), rank=rank, world_size=world)
             ctx.add_config("cylon.shuffle.peer", peer)
             assert ctx.get_rank() == rank and ctx.get_world_size() == world
-            results[rank] = run_checks(api, ctx, rank, world)
+            results[rank] = run_checks(api, ctx, rank, world, shared)
             ctx.barrier()
         except BaseException:
             errors.append("rank %d:\n%s" % (rank, traceback.format_exc()))
