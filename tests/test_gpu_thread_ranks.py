@@ -13,9 +13,11 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("world,peer", [(2, "1"), (3, "0"), (4, "1")])
-def test_distributed_operators_with_thread_ranks(world, peer):
-    p = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "thread_worker.py"), str(world), peer], capture_output=True, text=True,
+# world 4 runs the golden-file checks only (reference per-rank CSVs + python/test/test_dist_rl.py counts): four Python rank
+# threads share one interpreter lock, and the synthetic checks are already held at world 2 (peer stores) and 3 (general path)
+@pytest.mark.parametrize("world,peer,scope", [(2, "1", "all"), (3, "0", "all"), (4, "1", "golden")])
+def test_distributed_operators_with_thread_ranks(world, peer, scope):
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "thread_worker.py"), str(world), peer, scope], capture_output=True, text=True,
                        timeout=900, cwd=ROOT)
     assert p.returncode == 0, p.stdout[-3000:] + "\n" + p.stderr[-6000:]
     assert "THREAD_RANKS_OK world=%d peer=%s" % (world, peer) in p.stdout

@@ -1,6 +1,7 @@
 """Ranks as THREADS of this process on one GPU (cylon::net::ThreadConfig): the same checks as tests/dist_worker.py runs over
 NCCL, so that the distributed operators' host logic, count exchange, packing and the peer-store scatter are exercised at
-world > 1 on a single-GPU box. usage: thread_worker.py WORLD [PEER]"""
+world > 1 on a single-GPU box. usage: thread_worker.py WORLD [PEER] [golden]
+("golden": only the checks against the reference's per-rank golden files and known answers)"""
 import os
 import sys
 import threading
@@ -16,6 +17,7 @@ from tests.dist_checks import SharedExpectations, run_checks  # noqa: E402
 def main():
     world = int(sys.argv[1])
     peer = sys.argv[2] if len(sys.argv) > 2 else "1"
+    golden_only = len(sys.argv) > 3 and sys.argv[3] == "golden"
     results, errors = [0] * world, []
     shared = SharedExpectations()
 
@@ -24,7 +26,7 @@ def main():
             ctx = api.CylonContext(device=0, thread_group="ranks-%d" % os.getpid(), rank=rank, world_size=world)
             ctx.add_config("cylon.shuffle.peer", peer)
             assert ctx.get_rank() == rank and ctx.get_world_size() == world
-            results[rank] = run_checks(api, ctx, rank, world, shared)
+            results[rank] = run_checks(api, ctx, rank, world, shared, golden_only)
             ctx.barrier()
         except BaseException:
             errors.append("rank %d:\n%s" % (rank, traceback.format_exc()))
