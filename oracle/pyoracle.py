@@ -446,3 +446,143 @@ def distributed_hash_groupby(tables, idx_cols, agg_cols, agg_ops):
         shuffled = shuffle(local, idx_after)
         return [hash_groupby(t, idx_after, aggs) for t in shuffled]
     return local
+
+
+# ---- Sort / DistributedSort (table.cpp:291-382) and its range partitioning (arrow_partition_kernels.cpp:334-455) -------------
+def sort_sample_positions(n, num_samples):
+    """Rows the range partitioner looks at. The reference draws a random sample (util::SampleArray) unless num_samples equals the
+    row count, in which case it uses the whole column (arrow_partition_kernels.cpp:375-381); the product takes the rows
+    floor(i * n / num_samples) so that results repeat, and the whole column when num_samples >= n."""
+    if num_samples >= n:
+        return np.arange(n, dtype=np.int64)
+    return (np.arange(num_samples, dtype=np.int64) * n) // max(1, num_samples)
+
+
+def sort_bin_pos(vals, mn, mx, num_bins):
+    """get_bin_pos (arrow_partition_kernels.cpp:436-440) with the promotions C++ applies for each column type:
+    (val >= min) + ((val >= min) & (val < max)) * ((val - min) * num_bins / range) + (val >= max) * num_bins, range = (T)(max - min).
+    Where the reference is undefined (range == 0, NaN) the quotient counts as 0 and NaN goes to the last bin; the result is clamped
+    to the num_bins + 2 entries of bin_to_partition."""
+    vals = np.asarray(vals)
+    dt = vals.dtype
+    nb = int(num_bins)
+    ge_min, ge_max = vals >= mn, vals >= mx
+    mask = ge_min & (vals < mx)
+    with np.errstate(all="ignore"):
+        if dt.kind == "f":
+            f = dt.type
+            rng = f(f(mx) - f(mn))
+            q = (vals - f(mn)) * f(nb) / rng
+            q = np.where(mask, q, f(0))
+            total = (ge_min.astype(dt) + q) + (ge_max.astype(np.uint32) * np.uint32(nb)).astype(dt)
+            pos = np.where(np.isnan(vals), nb + 1, np.trunc(total)).astype(np.int64)
+        elif dt.itemsize <= 4:
+            # int / unsigned int arithmetic: the product with the uint32 num_bins and the division are unsigned 32-bit
+            wide = np.int64 if dt.kind == "i" else np.uint64
+            rng_t = np.array(int(mx) - int(mn)).astype(dt)          # narrowed to T like `range = max - min`
+            b = int(np.array(rng_t).astype(np.int32 if dt.kind == "i" else np.uint32).astype(np.uint32)) if dt.itemsize < 4 or dt.kind == "i" else int(rng_t)
+            a = ((vals.astype(wide) - wide(mn)).astype(np.int64) & 0xFFFFFFFF).astype(np.uint64)
+            a = (a * np.uint64(nb)) & np.uint64(0xFFFFFFFF)
+            q = a // np.uint64(b) if b else np.zeros_like(a)
+            q = np.where(mask, q, 0).astype(np.uint64)
+            pos = ((ge_min.astype(np.uint64) + q + ge_max.astype(np.uint64) * np.uint64(nb)) & np.uint64(0xFFFFFFFF)).astype(np.int64)
+        elif dt.kind == "i":
+            rng = np.int64(np.array(int(mx) - int(mn)).astype(np.int64)) if abs(int(mx) - int(mn)) < 2 ** 63 else np.array(int(mx) - int(mn) - 2 ** 64).astype(np.int64)
+            a = (vals.view(np.uint64) - np.uint64(np.int64(mn).view(np.uint64))) * np.uint64(nb)
+            a = a.view(np.int64)
+            q = np.zeros_like(a) if int(rng) == 0 else (np.abs(a) // abs(int(rng))) * np.sign(a) * (1 if int(rng) > 0 else -1)  # C division truncates
+            q = np.where(mask, q, 0)
+            pos = ge_min.astype(np.int64) + q + ge_max.astype(np.int64) * nb
+        else:
+            rng = np.uint64((int(mx) - int(mn)) % 2 ** 64)
+            a = (vals - np.uint64(mn)) * np.uint64(nb)
+            q = a // rng if int(rng) else np.zeros_like(a)
+            q = np.where(mask, q, 0)
+            pos = (ge_min.astype(np.uint64) + q + ge_max.astype(np.uint64) * np.uint64(nb)).astype(np.int64)
+    return np.clip(pos, 0, nb + 1)
+
+
+def sort_bin_to_partition(global_counts, total_samples, num_partitions):
+    """Quantile split of the sample histogram, in float like the reference (float_t; arrow_partition_kernels.cpp:412-427)."""
+    quantile = np.float32(1.0 / num_partitions)
+    prefix, target, curr = np.float32(0), quantile, 0
+    out = []
+    for c in global_counts:
+        out.append(curr)
+        freq = np.float32(np.float32(int(c)) / np.float32(int(total_samples))) if total_samples else np.float32(0)
+        prefix = np.float32(prefix + freq)
+        if prefix > target:
+            curr += 1 if curr < num_partitions - 1 else 0
+            target = np.float32(target + quantile)
+    return np.asarray(out, dtype=np.uint32)
+
+
+def map_to_sort_partitions(tables, col, ascending=True, num_samples=0, num_bins=0):
+    """MapToSortPartitions (partition/partition.cpp:168-198) + RangePartitionKernel on every rank at once -> (pid per rank, hist per rank).
+    num_samples == 0: 1 % of the rank's rows; num_bins == 0: 16 per partition. total_samples is the number of rows actually sampled
+    over all ranks (the reference multiplies ITS OWN num_samples by the world size, identical when the ranks hold equal row counts)."""
+    world = len(tables)
+    nb = num_bins if num_bins else world * 16
+    samples = []
+    for t in tables:
+        v = t[col].data
+        n = len(v)
+        k = num_samples if num_samples else min(int(n * 0.01), n)
+        samples.append(v[sort_sample_positions(n, k)])
+    nonempty = [s for s in samples if len(s)]
+    total = sum(len(s) for s in samples)
+    if not nonempty:  # nothing sampled: every row falls below "min" -> bin 0
+        pids = [np.full(len(t[col].data), 0 if ascending else world - 1, dtype=np.uint32) for t in tables]
+        return pids, [np.bincount(p, minlength=world).astype(np.uint32) for p in pids]
+    mn = min(s.min() for s in nonempty)
+    mx = max(s.max() for s in nonempty)
+    counts = np.zeros(nb + 2, dtype=np.uint64)
+    for s in nonempty:
+        counts += np.bincount(sort_bin_pos(s, mn, mx, nb), minlength=nb + 2).astype(np.uint64)
+    b2p = sort_bin_to_partition(counts, total, world)
+    pids = []
+    for t in tables:
+        p = b2p[sort_bin_pos(t[col].data, mn, mx, nb)]
+        pids.append((p if ascending else (world - 1 - p)).astype(np.uint32))
+    return pids, [np.bincount(p, minlength=world).astype(np.uint32) for p in pids]
+
+
+def _sort_key(c, ascending):
+    """order-preserving unsigned key; validity is ignored (the reference's sorters compare value slots)"""
+    v = c.data
+    if v.dtype.kind == "f":
+        u = v.view(np.uint32 if v.dtype.itemsize == 4 else np.uint64)
+        top = u.dtype.type(1) << u.dtype.type(u.dtype.itemsize * 8 - 1)
+        k = np.where(u & top, ~u, u | top)
+    elif v.dtype.kind == "i":
+        u = v.view("u%d" % v.dtype.itemsize)
+        k = u ^ (u.dtype.type(1) << u.dtype.type(u.dtype.itemsize * 8 - 1))
+    else:
+        k = v
+    return k if ascending else ~k
+
+
+def sort_table(table, sort_cols, directions):
+    """cylon::Sort (table.cpp:291-328): argsort by the sort columns (first column most significant), then Take -- which keeps the
+    source validity. Ties are in input order here (the reference's std::sort leaves them unspecified)."""
+    n = _nrows(table)
+    idx = np.arange(n, dtype=np.int64)
+    for c, asc in reversed(list(zip(sort_cols, directions))):
+        k = _sort_key(table[c], asc)
+        idx = idx[np.argsort(k[idx], kind="stable")]
+    out = take_table(table, idx)
+    for o, c in zip(out, table):
+        if c.validity is not None:
+            o.validity = np.packbits(c.valid_mask()[idx], bitorder="little")
+    return out
+
+
+def distributed_sort(tables, sort_cols, directions, num_samples=0, num_bins=0):
+    """cylon::DistributedSort (table.cpp:338-382): range-partition on the FIRST sort column, Split (drops validity, B2), all-to-all,
+    local sort by all sort columns."""
+    world = len(tables)
+    if world == 1:
+        return [sort_table(tables[0], sort_cols, directions)]
+    pids, _ = map_to_sort_partitions(tables, sort_cols[0], directions[0], num_samples, num_bins)
+    parts = [split(t, p, world) for t, p in zip(tables, pids)]
+    return [sort_table(concat_tables([parts[src][dst] for src in range(world)]), sort_cols, directions) for dst in range(world)]

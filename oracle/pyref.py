@@ -158,7 +158,7 @@ def _table_out(h):
     return out
 
 
-DIST_JOIN, DIST_UNION, DIST_SUBTRACT, DIST_INTERSECT, DIST_UNIQUE, DIST_SHUFFLE, DIST_GROUPBY = range(7)
+DIST_JOIN, DIST_UNION, DIST_SUBTRACT, DIST_INTERSECT, DIST_UNIQUE, DIST_SHUFFLE, DIST_GROUPBY, DIST_SORT, MAP_SORT_PARTITIONS, LOCAL_SORT = range(10)
 
 
 def dist_op(op, lefts, rights=None, p1=(), p2=(), join_type=0, algorithm=0, rows_only=False):

@@ -7,6 +7,7 @@
 
 #include <cstdint>
 #include <cstring>
+#include <limits>
 #include <memory>
 #include <vector>
 
@@ -31,15 +32,11 @@
 #include "compute/aggregates.hpp"
 #include "join/join_config.hpp"
 #include "net/mpi/mpi_operations.hpp"
+#include "partition/partition.hpp"
 #include "util/arrow_utils.hpp"
 
 // ---- link-time stand-ins for reference functions that are reachable but never called by the checker ----------
 namespace cylon {
-namespace mpi {
-cylon::Status AllReduce(const void *, void *, int, const std::shared_ptr<DataType> &, cylon::net::ReduceOp) {
-  return cylon::Status(cylon::Code::NotImplemented, "no MPI in the checker build");
-}
-}  // namespace mpi
 arrow::MemoryPool *ToArrowPool(const std::shared_ptr<cylon::CylonContext> &) { return arrow::default_memory_pool(); }
 // The context without MPI (ctx/cylon_context.cpp pulls in the MPI communicator): same observable behaviour for the
 // members the table operators use.
@@ -82,12 +79,6 @@ std::shared_ptr<cylon::DataType> ToCylonType(const std::shared_ptr<arrow::DataTy
 bool validateArrowTableTypes(const std::shared_ptr<arrow::Table> &) { return true; }
 std::shared_ptr<arrow::DataType> convertToArrowType(const std::shared_ptr<DataType> &, int32_t, int32_t, int32_t) { return nullptr; }
 }  // namespace tarrow
-namespace compute {
-cylon::Status MinMax(std::shared_ptr<cylon::CylonContext> &, const arrow::Datum &, const std::shared_ptr<cylon::DataType> &,
-                     std::shared_ptr<cylon::compute::Result> &) {
-  return cylon::Status(cylon::Code::NotImplemented, "not part of the checker build");
-}
-}  // namespace compute
 }  // namespace cylon
 
 namespace {
@@ -310,7 +301,28 @@ struct MemHub {
       cv.wait(lk, [&] { return generation != gen; });
     }
   }
+  // every rank deposits n bytes and gets everybody's (what MPI_Allreduce / MPI_Allgather carry in the reference)
+  std::vector<std::vector<uint8_t>> slots;
+  std::vector<std::vector<uint8_t>> exchange(int rank, const void *p, size_t n) {
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      if ((int)slots.size() != world) slots.resize((size_t)world);
+      const uint8_t *b = static_cast<const uint8_t *>(p);
+      slots[(size_t)rank].assign(b, b + n);
+    }
+    barrier();
+    std::vector<std::vector<uint8_t>> all;
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      all = slots;
+    }
+    barrier();
+    return all;
+  }
 };
+// the rank thread's hub: mpi::AllReduce has no context argument (MPI_COMM_WORLD in the reference)
+thread_local MemHub *t_hub = nullptr;
+thread_local int t_rank = 0;
 
 class MemChannel : public cylon::Channel {
  public:
@@ -455,14 +467,128 @@ class MemCommunicator : public cylon::net::Communicator {
   MemHub *hub_;
 };
 
+// element-wise reduction over what every rank deposited (net/mpi/mpi_operations.cpp:24-90 maps the same DataTypes and ops onto MPI)
+template <typename T>
+void reduce_ranks(const std::vector<std::vector<uint8_t>> &all, void *out, int count, cylon::net::ReduceOp op) {
+  T *o = static_cast<T *>(out);
+  for (int i = 0; i < count; i++) {
+    T acc;
+    std::memcpy(&acc, all[0].data() + (size_t)i * sizeof(T), sizeof(T));
+    for (size_t r = 1; r < all.size(); r++) {
+      T v;
+      std::memcpy(&v, all[r].data() + (size_t)i * sizeof(T), sizeof(T));
+      switch (op) {
+        case cylon::net::SUM: acc = (T)(acc + v); break;
+        case cylon::net::MIN: acc = v < acc ? v : acc; break;
+        case cylon::net::MAX: acc = v > acc ? v : acc; break;
+      }
+    }
+    o[i] = acc;
+  }
+}
+
+template <typename ARROW_T>
+cylon::Status minmax_typed(const arrow::Datum &input, std::shared_ptr<cylon::compute::Result> &output) {
+  using S = typename arrow::TypeTraits<ARROW_T>::ScalarType;
+  using A = typename arrow::TypeTraits<ARROW_T>::ArrayType;
+  using T = typename ARROW_T::c_type;
+  arrow::ArrayVector chunks;
+  if (input.is_chunked_array()) chunks = input.chunked_array()->chunks();
+  else chunks.push_back(input.make_array());
+  // nulls skipped (MinMaxOptions::SKIP in the reference); an empty input gives (max, lowest) like arrow's kernel state
+  T mm[2] = {std::numeric_limits<T>::max(), std::numeric_limits<T>::lowest()};
+  for (const auto &c : chunks) {
+    const auto arr = std::static_pointer_cast<A>(c);
+    for (int64_t i = 0; i < arr->length(); i++) {
+      if (arr->IsNull(i)) continue;
+      const T v = arr->Value(i);
+      if (v < mm[0]) mm[0] = v;
+      if (v > mm[1]) mm[1] = v;
+    }
+  }
+  if (t_hub && t_hub->world > 1) {
+    const auto all = t_hub->exchange(t_rank, mm, sizeof(mm));
+    for (const auto &b : all) {
+      T v[2];
+      std::memcpy(v, b.data(), sizeof(v));
+      if (v[0] < mm[0]) mm[0] = v[0];
+      if (v[1] > mm[1]) mm[1] = v[1];
+    }
+  }
+  auto st = arrow::StructScalar::Make({std::make_shared<S>(mm[0]), std::make_shared<S>(mm[1])}, {"min", "max"});
+  if (!st.ok()) return cylon::Status(cylon::Code::ExecutionError, st.status().message());
+  output = std::make_shared<cylon::compute::Result>(arrow::Datum(st.ValueOrDie()));
+  return cylon::Status::OK();
+}
+
 }  // namespace
+
+// ---- stand-ins for the two MPI-backed functions DistributedSort's range partitioning calls (NOT reference code: the
+// reference's compute/aggregates.cpp and net/mpi/mpi_operations.cpp need MPI). Same contract, ranks = threads of this process.
+namespace cylon {
+namespace mpi {
+cylon::Status AllReduce(const void *send_buf, void *rcv_buf, int count, const std::shared_ptr<DataType> &data_type, cylon::net::ReduceOp op) {
+  int w = 0;
+  switch (data_type->getType()) {
+    case Type::UINT8: case Type::INT8: w = 1; break;
+    case Type::UINT16: case Type::INT16: w = 2; break;
+    case Type::UINT32: case Type::INT32: case Type::FLOAT: w = 4; break;
+    case Type::UINT64: case Type::INT64: case Type::DOUBLE: w = 8; break;
+    default: return cylon::Status(cylon::Code::NotImplemented, "AllReduce: type not supported by the checker");
+  }
+  std::vector<std::vector<uint8_t>> all;
+  if (t_hub && t_hub->world > 1) {
+    all = t_hub->exchange(t_rank, send_buf, (size_t)count * w);
+  } else {
+    const uint8_t *b = static_cast<const uint8_t *>(send_buf);
+    all.emplace_back(b, b + (size_t)count * w);
+  }
+  switch (data_type->getType()) {
+    case Type::UINT8: reduce_ranks<uint8_t>(all, rcv_buf, count, op); break;
+    case Type::INT8: reduce_ranks<int8_t>(all, rcv_buf, count, op); break;
+    case Type::UINT16: reduce_ranks<uint16_t>(all, rcv_buf, count, op); break;
+    case Type::INT16: reduce_ranks<int16_t>(all, rcv_buf, count, op); break;
+    case Type::UINT32: reduce_ranks<uint32_t>(all, rcv_buf, count, op); break;
+    case Type::INT32: reduce_ranks<int32_t>(all, rcv_buf, count, op); break;
+    case Type::UINT64: reduce_ranks<uint64_t>(all, rcv_buf, count, op); break;
+    case Type::INT64: reduce_ranks<int64_t>(all, rcv_buf, count, op); break;
+    case Type::FLOAT: reduce_ranks<float>(all, rcv_buf, count, op); break;
+    default: reduce_ranks<double>(all, rcv_buf, count, op); break;
+  }
+  return cylon::Status::OK();
+}
+}  // namespace mpi
+namespace compute {
+// local min / max (nulls skipped), then min / max over the ranks -- what compute/aggregates.cpp:82-152 does
+cylon::Status MinMax(std::shared_ptr<cylon::CylonContext> &, const arrow::Datum &array, const std::shared_ptr<cylon::DataType> &,
+                     std::shared_ptr<cylon::compute::Result> &output) {
+  const arrow::Datum &local = array;
+  switch (array.type()->id()) {
+    case arrow::Type::UINT8: return minmax_typed<arrow::UInt8Type>(local, output);
+    case arrow::Type::INT8: return minmax_typed<arrow::Int8Type>(local, output);
+    case arrow::Type::UINT16: return minmax_typed<arrow::UInt16Type>(local, output);
+    case arrow::Type::INT16: return minmax_typed<arrow::Int16Type>(local, output);
+    case arrow::Type::UINT32: return minmax_typed<arrow::UInt32Type>(local, output);
+    case arrow::Type::INT32: return minmax_typed<arrow::Int32Type>(local, output);
+    case arrow::Type::UINT64: return minmax_typed<arrow::UInt64Type>(local, output);
+    case arrow::Type::INT64: return minmax_typed<arrow::Int64Type>(local, output);
+    case arrow::Type::FLOAT: return minmax_typed<arrow::FloatType>(local, output);
+    case arrow::Type::DOUBLE: return minmax_typed<arrow::DoubleType>(local, output);
+    default: return cylon::Status(cylon::Code::NotImplemented, "MinMax: type not supported by the checker");
+  }
+}
+}  // namespace compute
+}  // namespace cylon
 
 extern "C" {
 
 // One Distributed* operator of the reference on `world` ranks (threads). lcols / rcols: world x nlc / world x nrc column
 // descriptors, rank-major. op: 0 DistributedJoin(p1 = left keys, p2 = right keys, join_type, algorithm, prefixes l_/r_),
 // 1/2/3 DistributedUnion/Subtract/Intersect, 4 DistributedUnique(p1 = columns), 5 Shuffle(p1 = hash columns),
-// 6 DistributedHashGroupBy(p1 = index columns, p2 = (aggregate column, AggregationOpId) pairs flattened).
+// 6 DistributedHashGroupBy(p1 = index columns, p2 = (aggregate column, AggregationOpId) pairs flattened),
+// 7 DistributedSort(p1 = sort columns, p2 = directions (1 = ascending), join_type = num_bins, algorithm = num_samples; -1 = the
+//   rank's row count, i.e. no sampling), 8 MapToSortPartitions(column p1[0], ascending = p2[0], same options) -> one uint32
+//   column of target partitions per rank, 9 Sort(p1 = sort columns, p2 = directions), rank-local.
 // out: `world` result tables (ref_table_*), in rank order. Returns the first non-zero cylon::Code, or 0.
 int ref_dist_op(int32_t op, int32_t world, const ref_col_in *lcols, int32_t nlc, const ref_col_in *rcols, int32_t nrc, const int32_t *p1,
                 int32_t n1, const int32_t *p2, int32_t n2, int32_t join_type, int32_t algorithm, ref_table **out) {
@@ -471,6 +597,8 @@ int ref_dist_op(int32_t op, int32_t world, const ref_col_in *lcols, int32_t nlc,
   std::vector<int> codes((size_t)world, 0);
   std::vector<std::shared_ptr<arrow::Table>> results((size_t)world);
   auto body = [&](int r) {
+    t_hub = &hub;
+    t_rank = r;
     auto ctx = std::make_shared<cylon::CylonContext>(world > 1);
     if (world > 1) ctx->setCommunicator(std::make_shared<MemCommunicator>(&hub, r));
     std::shared_ptr<cylon::Table> left, right, res;
@@ -508,6 +636,30 @@ int ref_dist_op(int32_t op, int32_t world, const ref_col_in *lcols, int32_t nlc,
           agg_ops.push_back(static_cast<cylon::compute::AggregationOpId>(p2[i + 1]));
         }
         st = cylon::DistributedHashGroupBy(left, std::vector<int32_t>(p1, p1 + n1), agg_cols, agg_ops, res);
+        break;
+      }
+      case 7:
+      case 8:
+      case 9: {
+        std::vector<bool> dirs;
+        for (int i = 0; i < n2; i++) dirs.push_back(p2[i] != 0);
+        const uint64_t samples = algorithm < 0 ? (uint64_t)left->Rows() : (uint64_t)algorithm;
+        if (op == 7) {
+          st = cylon::DistributedSort(left, v1, res, dirs, cylon::SortOptions{(uint32_t)join_type, samples});
+        } else if (op == 9) {
+          st = cylon::Sort(left, std::vector<int32_t>(v1.begin(), v1.end()), res, dirs);
+        } else {
+          std::vector<uint32_t> target, hist;
+          st = cylon::MapToSortPartitions(left, v1[0], (uint32_t)world, target, hist, dirs[0], samples, (uint32_t)join_type);
+          if (st.is_ok()) {
+            arrow::UInt32Builder b;
+            (void)b.AppendValues(target);
+            std::shared_ptr<arrow::Array> arr;
+            (void)b.Finish(&arr);
+            auto t = arrow::Table::Make(arrow::schema({arrow::field("pid", arrow::uint32())}), {arr});
+            st = cylon::Table::FromArrowTable(ctx, t, res);
+          }
+        }
         break;
       }
       default: st = cylon::Status(cylon::Code::Invalid, "unknown op");
