@@ -325,6 +325,29 @@ class Table:
     def distributed_unique(self, columns):
         return self.unique(columns, True)
 
+    def sort(self, columns, ascending=True, distributed=False, num_bins=0, num_samples=0):
+        """cylon::Sort / DistributedSort (table.hpp:353-404): columns[0] most significant; ascending: bool or one per column"""
+        columns = [columns] if isinstance(columns, int) else list(columns)
+        dirs = [ascending] * len(columns) if isinstance(ascending, bool) else list(ascending)
+        cols = (C.c_int32 * len(columns))(*columns)
+        asc = (C.c_int32 * len(columns))(*[1 if d else 0 for d in dirs])
+        h = C.c_void_p()
+        check(lib().cylon_sort(self._h, cols, asc, C.c_int32(len(columns)), C.c_int32(1 if distributed else 0), C.c_uint32(num_bins),
+                               C.c_uint64(num_samples), C.byref(h)))
+        return Table(h, self.ctx)
+
+    def distributed_sort(self, columns, ascending=True, num_bins=0, num_samples=0):
+        return self.sort(columns, ascending, True, num_bins, num_samples)
+
+    def map_to_sort_partitions(self, column, num_partitions, ascending=True, num_samples=0, num_bins=0):
+        """cylon::MapToSortPartitions -> (target partition per row, rows per partition) as numpy arrays; collective"""
+        pid = np.zeros(self.row_count, dtype=np.uint32)
+        hist = np.zeros(num_partitions, dtype=np.uint32)
+        check(lib().cylon_map_to_sort_partitions(self._h, C.c_int32(column), C.c_uint32(num_partitions), C.c_int32(1 if ascending else 0),
+                                                 C.c_uint64(num_samples), C.c_uint32(num_bins), pid.ctypes.data_as(C.c_void_p),
+                                                 hist.ctypes.data_as(C.c_void_p)))
+        return pid, hist
+
     def shuffle(self, hash_columns):
         cols = (C.c_int32 * len(hash_columns))(*hash_columns)
         h = C.c_void_p()

@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256) digit_hist_kernel(const uint64_t *__restr
 
 // Sorts (tags, ids) ascending by tag (stable). On return *tags_io / *ids_io point at the sorted buffers (either
 // the given ones or the temporaries). Synchronises the stream once (digit histogram readback).
-static int radix_sort_pairs(uint64_t **tags_io, uint32_t **ids_io, uint64_t **tags_tmp, uint32_t **ids_tmp, int64_t n, cudaStream_t s) {
+int radix_sort_pairs(uint64_t **tags_io, uint32_t **ids_io, uint64_t **tags_tmp, uint32_t **ids_tmp, int64_t n, cudaStream_t s) {
   if (n <= 1) return CYL_OK;
   Scratch hist;
   CYL_TRY(hist.alloc(8 * 256 * sizeof(unsigned long long), s));

@@ -2,10 +2,12 @@
 // reference's string-id facade cpp/src/cylon/table_api.cpp:117+ that its JNI and Cython bindings call.
 #include "cylon_b200_api.h"
 
+#include <algorithm>
 #include <cstdarg>
 #include <cstring>
 
 #include "cylon/groupby/groupby.hpp"
+#include "cylon/partition/partition.hpp"
 #include "cylon/table.hpp"
 #include "util.hpp"
 
@@ -196,6 +198,31 @@ int cylon_shuffle(cylon_table_t *t, const int32_t *cols, int32_t ncols, cylon_ta
   Status st = cylon::Shuffle(t->table, c, o);
   if (!st.is_ok()) return report(st);
   *out = wrap(o);
+  return CYL_OK;
+}
+
+int cylon_sort(cylon_table_t *t, const int32_t *sort_cols, const int32_t *ascending, int32_t ncols, int32_t distributed, uint32_t num_bins,
+               uint64_t num_samples, cylon_table_t **out) {
+  if (!t) return cylb::fail(CYL_KeyError, "Couldn't find the table");
+  if (ncols < 1 || !sort_cols || !ascending) return cylb::fail(CYL_Invalid, "cylon_sort: needs at least one sort column and its direction");
+  std::vector<bool> dirs;
+  for (int32_t i = 0; i < ncols; i++) dirs.push_back(ascending[i] != 0);
+  std::shared_ptr<cylon::Table> o;
+  Status st = distributed ? cylon::DistributedSort(t->table, std::vector<int>(sort_cols, sort_cols + ncols), o, dirs, cylon::SortOptions{num_bins, num_samples})
+                          : cylon::Sort(t->table, std::vector<int32_t>(sort_cols, sort_cols + ncols), o, dirs);
+  if (!st.is_ok()) return report(st);
+  *out = wrap(o);
+  return CYL_OK;
+}
+
+int cylon_map_to_sort_partitions(cylon_table_t *t, int32_t column, uint32_t num_partitions, int32_t ascending, uint64_t num_samples, uint32_t num_bins,
+                                 uint32_t *target_partitions, uint32_t *partition_hist) {
+  if (!t) return cylb::fail(CYL_KeyError, "Couldn't find the table");
+  std::vector<uint32_t> pid, hist;
+  Status st = cylon::MapToSortPartitions(t->table, column, num_partitions, pid, hist, ascending != 0, num_samples, num_bins);
+  if (!st.is_ok()) return report(st);
+  if (target_partitions) std::copy(pid.begin(), pid.end(), target_partitions);
+  if (partition_hist) std::copy(hist.begin(), hist.end(), partition_hist);
   return CYL_OK;
 }
 

@@ -188,7 +188,10 @@ Status MapToHashPartitions(const std::shared_ptr<Table> &table, int32_t hash_col
   return MapToHashPartitions(table, std::vector<int32_t>{hash_column_idx}, num_partitions, target_partitions, partition_hist);
 }
 
-Status Split(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *target_partitions, std::vector<std::shared_ptr<Table>> &output) {
+// Split by given partition ids: the partition-ordered copy of the table and the partition boundaries (host). Row order inside a
+// partition = input order.
+static Status PartitionTableByPid(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *target_partitions, Partitioned *out) {
+  Partitioned &pt = *out;
   auto ctx = table->GetContext();
   void *stream = ctx->GetStream();
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -197,7 +200,7 @@ Status Split(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *ta
   RETURN_CYLON_STATUS_IF_FAILED(dest.alloc((size_t)(n + 1) * 8, stream));
   RETURN_CYLON_STATUS_IF_FAILED(part_offsets.alloc((P + 1) * 8, stream));
   CYL_RETURN_IF_FAILED(cyl_scatter_map(target_partitions, n, P, dest.as<int64_t>(), part_offsets.as<int64_t>(), stream));
-  Partitioned pt;
+  pt.cols.clear();
   pt.byte_off.assign((size_t)table->Columns(), {});
   for (const auto &c : table->GetColumns()) {
     const cyl_column_t &src = c->desc();
@@ -215,7 +218,14 @@ Status Split(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *ta
   pt.row_off.assign(P + 1, 0);
   CUDA_RETURN_IF_FAILED(cudaMemcpyAsync(pt.row_off.data(), part_offsets.p, (P + 1) * 8, cudaMemcpyDeviceToHost, s));
   CUDA_RETURN_IF_FAILED(cudaStreamSynchronize(s));
-  RETURN_CYLON_STATUS_IF_FAILED(BoundaryByteOffsets(pt.cols, part_offsets.as<int64_t>(), P, stream, &pt.byte_off));
+  return BoundaryByteOffsets(pt.cols, part_offsets.as<int64_t>(), P, stream, &pt.byte_off);
+}
+
+Status Split(const std::shared_ptr<Table> &table, uint32_t P, const uint32_t *target_partitions, std::vector<std::shared_ptr<Table>> &output) {
+  auto ctx = table->GetContext();
+  void *stream = ctx->GetStream();
+  Partitioned pt;
+  RETURN_CYLON_STATUS_IF_FAILED(PartitionTableByPid(table, P, target_partitions, &pt));
   output.clear();
   std::vector<std::unique_ptr<DevBuf>> vbytes;
   RETURN_CYLON_STATUS_IF_FAILED(UnpackValidity(pt, stream, &vbytes));
@@ -420,21 +430,24 @@ static Status ShufflePeerScatter(std::shared_ptr<CylonContext> &ctx, std::shared
   return Status::OK();
 }
 
+// given_pid (device, one target rank per row; may be null): route by these ids instead of hashing hash_cols -- the range
+// partitioning of DistributedSort. Such tables take the general path.
 static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &table, const std::vector<int> &hash_cols,
-                               std::shared_ptr<Table> &out) {
+                               std::shared_ptr<Table> &out, const uint32_t *given_pid = nullptr) {
   auto comm = ctx->GetCommunicator();
   const int P = ctx->GetWorldSize(), rank = ctx->GetRank();
   void *stream = ctx->GetStream();
   const int ncols = table->Columns();
 
-  {
+  if (!given_pid) {
     bool handled = false;
     RETURN_CYLON_STATUS_IF_FAILED(ShufflePeerScatter(ctx, table, hash_cols, out, &handled));
     if (handled) return Status::OK();
   }
   detail::StageTrace trace("shuffle", stream);
   Partitioned pt;
-  RETURN_CYLON_STATUS_IF_FAILED(PartitionTable(table, hash_cols, (uint32_t)P, &pt));
+  if (given_pid) RETURN_CYLON_STATUS_IF_FAILED(PartitionTableByPid(table, (uint32_t)P, given_pid, &pt));
+  else RETURN_CYLON_STATUS_IF_FAILED(PartitionTable(table, hash_cols, (uint32_t)P, &pt));
   trace.mark("partition");
   std::vector<std::string> names = table->ColumnNames();
   std::vector<int> has_validity(ncols);
@@ -560,6 +573,12 @@ static Status ShuffleByHashing(std::shared_ptr<CylonContext> &ctx, std::shared_p
   out = std::make_shared<Table>(std::move(out_cols), ctx);
   return Status::OK();
 }
+
+namespace detail {
+Status ShuffleByPartitionIds(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &table, const uint32_t *target_ranks, std::shared_ptr<Table> &out) {
+  return ShuffleByHashing(ctx, table, {}, out, target_ranks);
+}
+}  // namespace detail
 
 Status Shuffle(std::shared_ptr<Table> &table, const std::vector<int> &hash_columns, std::shared_ptr<Table> &output) {  // table.cpp:910-921
   if (table == nullptr) return Status(Code::KeyError, "Couldn't find the table");

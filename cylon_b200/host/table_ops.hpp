@@ -24,6 +24,9 @@ Status FilterTable(const std::shared_ptr<Table> &t, const uint8_t *mask, std::sh
 // arrow::ConcatenateTables + CombineChunks of two tables with the same schema
 Status ConcatTables(const std::shared_ptr<Table> &a, const std::shared_ptr<Table> &b, std::shared_ptr<Table> *out);
 Status VerifyTableSchema(const Table &a, const Table &b);
+// all-to-all of a table whose rows already know their target rank (device uint32 per row): Split + exchange, chunks ordered by
+// source rank, row order inside a chunk = input order (host/shuffle.cpp)
+Status ShuffleByPartitionIds(std::shared_ptr<CylonContext> &ctx, std::shared_ptr<Table> &table, const uint32_t *target_ranks, std::shared_ptr<Table> &out);
 
 }  // namespace detail
 }  // namespace cylon

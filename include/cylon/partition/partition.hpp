@@ -27,12 +27,21 @@ Status Split(const std::shared_ptr<Table> &table, uint32_t num_partitions, const
 Status PartitionByHashing(const std::shared_ptr<Table> &table, const std::vector<int32_t> &hash_cols, uint32_t num_partitions,
                           std::vector<std::shared_ptr<Table>> &partitions);
 
+// Range partitioning for DistributedSort (partition/partition.hpp:60-74; partition.cpp:168-198): target partition of every row
+// by the value of one numeric column. COLLECTIVE when the table's context is distributed (min/max and the sample histogram are
+// reduced over the ranks). num_samples == 0: 1 % of the rows; num_bins == 0: 16 per partition. The sample is rows
+// floor(i * rows / num_samples) (the reference draws it at random unless num_samples == rows).
+Status MapToSortPartitions(const std::shared_ptr<Table> &table, int32_t column_idx, uint32_t num_partitions, std::vector<uint32_t> &target_partitions,
+                           std::vector<uint32_t> &partition_hist, bool ascending = true, uint64_t num_samples = 0, uint32_t num_bins = 0);
+
 // ---- device forms. target_partitions: device uint32[rows]; partition_hist: device uint64[num_partitions]. Both are
 // allocated by the callee (cyl_malloc'ed; release with cyl_free).
 Status MapToHashPartitions(const std::shared_ptr<Table> &table, const std::vector<int32_t> &hash_column_idx, uint32_t num_partitions,
                            uint32_t **target_partitions, uint64_t **partition_hist);
 Status MapToHashPartitions(const std::shared_ptr<Table> &table, int32_t hash_column_idx, uint32_t num_partitions,
                            uint32_t **target_partitions, uint64_t **partition_hist);
+Status MapToSortPartitions(const std::shared_ptr<Table> &table, int32_t column_idx, uint32_t num_partitions, uint32_t **target_partitions,
+                           uint64_t **partition_hist, bool ascending = true, uint64_t num_samples = 0, uint32_t num_bins = 0);
 // stable split by device partition ids into num_partitions tables (row order inside a partition = input order)
 Status Split(const std::shared_ptr<Table> &table, uint32_t num_partitions, const uint32_t *target_partitions,
              std::vector<std::shared_ptr<Table>> &output);

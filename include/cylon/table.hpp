@@ -75,6 +75,23 @@ Status HashPartition(std::shared_ptr<Table> &table, const std::vector<int> &hash
 Status Unique(std::shared_ptr<Table> &in, const std::vector<int> &cols, std::shared_ptr<Table> &out, bool first = true);
 Status DistributedUnique(std::shared_ptr<Table> &in, const std::vector<int> &cols, std::shared_ptr<Table> &out);
 
+// --- sort (table.hpp:353-404; table.cpp:291-382). Sort columns: numeric / temporal. Ties keep their input order; floats order
+// by IEEE total order; validity is carried along and not looked at (as the reference's sorters). ----------------------------
+Status Sort(std::shared_ptr<Table> &table, int sort_column, std::shared_ptr<Table> &output, bool ascending = true);
+Status Sort(std::shared_ptr<Table> &table, const std::vector<int32_t> &sort_columns, std::shared_ptr<Table> &out, bool ascending);
+Status Sort(std::shared_ptr<Table> &table, const std::vector<int32_t> &sort_columns, std::shared_ptr<Table> &out, const std::vector<bool> &sort_direction);
+struct SortOptions {  // 0 = default: num_bins = 16 per rank, num_samples = 1 % of the rank's rows (partition.cpp:181-182)
+  uint32_t num_bins;
+  uint64_t num_samples;
+  static SortOptions Defaults() { return {0, 0}; }
+};
+// Range-partitions on the FIRST sort column (sample -> min/max and bin histogram over all ranks -> quantile split), shuffles, sorts
+// locally by all sort columns: rank r holds a sorted run and every value of rank r orders before (ascending) those of rank r + 1.
+Status DistributedSort(std::shared_ptr<Table> &table, int sort_column, std::shared_ptr<Table> &output, bool ascending = true,
+                       SortOptions sort_options = SortOptions::Defaults());
+Status DistributedSort(std::shared_ptr<Table> &table, const std::vector<int> &sort_columns, std::shared_ptr<Table> &output,
+                       const std::vector<bool> &sort_direction, SortOptions sort_options = SortOptions::Defaults());
+
 // order-independent checksum of a table (no counterpart in the reference; used to compare full-size results)
 Status TableChecksum(const std::shared_ptr<Table> &table, uint64_t *checksum);
 

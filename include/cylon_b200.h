@@ -302,6 +302,36 @@ int cyl_lengths_to_offsets(const int32_t *lengths, int64_t n, int32_t *offsets, 
 int cyl_shuffle_plan(const int64_t *counts /* host */, int32_t world, int32_t rank, int64_t *send_off, int64_t *send_cnt, int64_t *recv_off,
                      int64_t *recv_cnt, int64_t *total_recv);
 
+/* ---------------------------------------------------------------- D: sort --------------------- */
+/* Row order of a table sorted by `nkeys` columns (keys[0] most significant; ascending[c] != 0: ascending): out_idx[i] = the row
+ * that comes i-th. Stable LSD radix sort of order-preserving 64-bit keys, one column per round from the last to the first.
+ * Sort columns: numeric / temporal values of at most 8 bytes (else CYL_NotImplemented). Validity is not looked at, as in the
+ * reference; floats order by IEEE total order (-0.0 before +0.0, NaN after +inf). Rows that tie on every column keep their input
+ * order (the reference's std::sort leaves them unspecified). Replaces SortIndices / SortIndicesMultiColumns
+ * (arrow/arrow_kernels.cpp:294-303,412-457) under Sort (table.cpp:291-328, util/arrow_utils.cpp:30-118); the Take that follows
+ * is cyl_gather_*. Synchronises. */
+int cyl_sort_indices(const cyl_column_t *keys /* host array */, int32_t nkeys, const int32_t *ascending /* host array */, int64_t nrows,
+                     int64_t *out_idx /* device, nrows */, void *stream);
+/* The range partitioner of DistributedSort: RangePartitionKernel (arrow/arrow_partition_kernels.cpp:334-455) under
+ * MapToSortPartitions (partition/partition.cpp:168-198), in three calls with the cross-rank reductions between them
+ * (compute::MinMax and mpi::AllReduce in the reference, :384-407):
+ *   1. cyl_range_sample_minmax: min and max of this rank's sample as ORDER KEYS (64-bit values whose unsigned order is the value
+ *      order, so every rank reduces them with plain unsigned min / max) and the number of sampled non-NaN values. The sample is
+ *      rows floor(i * nrows / num_samples), i < num_samples, or every row when num_samples >= nrows (the reference samples at
+ *      random unless num_samples == nrows).
+ *   2. cyl_range_sample_histogram: the sample counted into num_bins + 2 bins by get_bin_pos (:436-440), evaluated in the
+ *      column's own C++ type as the reference's template does (host out, to be summed over the ranks).
+ *   3. cyl_range_partition: target partition of EVERY row, bin_to_partition[get_bin_pos(value)] (num_partitions - 1 - that
+ *      when descending), and the rows per partition. total_samples <= 0 (nothing sampled on any rank) sends every row to bin 0.
+ * All three synchronise. */
+int cyl_range_sample_minmax(const cyl_column_t *col, int64_t nrows, int64_t num_samples, uint64_t *min_key /* host out */,
+                            uint64_t *max_key /* host out */, int64_t *count /* host out */, void *stream);
+int cyl_range_sample_histogram(const cyl_column_t *col, int64_t nrows, int64_t num_samples, uint64_t min_key, uint64_t max_key, uint32_t num_bins,
+                               uint64_t *hist /* host out, num_bins + 2 */, void *stream);
+int cyl_range_partition(const cyl_column_t *col, int64_t nrows, uint64_t min_key, uint64_t max_key, int64_t total_samples, uint32_t num_bins,
+                        const uint32_t *bin_to_partition /* host array, num_bins + 2 */, uint32_t num_partitions, int32_t ascending,
+                        uint32_t *pid /* device out, nrows */, uint64_t *partition_hist /* device out, num_partitions; may be NULL */, void *stream);
+
 /* ---------------------------------------------------------------- checks ----------------------- */
 /* Order-independent checksum of a table: sum over rows of a 64-bit mix of the row's values (nulls count as
  * zero bits + validity 0). No counterpart in the reference; it is how full-size results are compared with the

@@ -66,6 +66,14 @@ int cylon_set_operation(cylon_table_t *left, cylon_table_t *right, int32_t op, i
 int cylon_unique(cylon_table_t *t, const int32_t *cols, int32_t ncols, int32_t distributed, cylon_table_t **out);
 /* Shuffle (table.hpp:339). */
 int cylon_shuffle(cylon_table_t *t, const int32_t *hash_cols, int32_t ncols, cylon_table_t **out);
+/* Sort / DistributedSort (table.hpp:353-404): sort_cols[0] is the most significant column, ascending[c] != 0 = ascending.
+ * num_bins / num_samples = SortOptions (0 = defaults: 16 bins per rank, 1 % of the rank's rows). */
+int cylon_sort(cylon_table_t *t, const int32_t *sort_cols, const int32_t *ascending, int32_t ncols, int32_t distributed, uint32_t num_bins,
+               uint64_t num_samples, cylon_table_t **out);
+/* MapToSortPartitions (partition/partition.hpp:60-74): target partition per row and rows per partition into HOST arrays of
+ * rows / num_partitions entries. Collective on a distributed context. */
+int cylon_map_to_sort_partitions(cylon_table_t *t, int32_t column, uint32_t num_partitions, int32_t ascending, uint64_t num_samples, uint32_t num_bins,
+                                 uint32_t *target_partitions /* host out */, uint32_t *partition_hist /* host out */);
 /* HashPartition (table.hpp:348): out must hold num_partitions handles. */
 int cylon_hash_partition(cylon_table_t *t, const int32_t *hash_cols, int32_t ncols, int32_t num_partitions, cylon_table_t **out);
 /* HashGroupBy / DistributedHashGroupBy (groupby/groupby.hpp:23-33). ops: cyl_agg_op_t per aggregate column. */

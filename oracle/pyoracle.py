@@ -517,11 +517,11 @@ def sort_bin_to_partition(global_counts, total_samples, num_partitions):
     return np.asarray(out, dtype=np.uint32)
 
 
-def map_to_sort_partitions(tables, col, ascending=True, num_samples=0, num_bins=0):
+def map_to_sort_partitions(tables, col, ascending=True, num_samples=0, num_bins=0, num_partitions=None):
     """MapToSortPartitions (partition/partition.cpp:168-198) + RangePartitionKernel on every rank at once -> (pid per rank, hist per rank).
     num_samples == 0: 1 % of the rank's rows; num_bins == 0: 16 per partition. total_samples is the number of rows actually sampled
     over all ranks (the reference multiplies ITS OWN num_samples by the world size, identical when the ranks hold equal row counts)."""
-    world = len(tables)
+    world = num_partitions if num_partitions else len(tables)  # partitions; the ranks are len(tables)
     nb = num_bins if num_bins else world * 16
     samples = []
     for t in tables:
