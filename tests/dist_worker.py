@@ -33,7 +33,12 @@ def main():
     assert ctx.get_rank() == rank and ctx.get_world_size() == world
     peer = os.environ.get("CYLON_TEST_SHUFFLE_PEER", "1")
     ctx.add_config("cylon.shuffle.peer", peer)  # "0": every shuffle takes the NCCL send/recv path, also for fixed-width tables
-    checks = run_checks(api, ctx, rank, world)
+    if os.environ.get("CYLON_TEST_SCOPE") == "sort":  # Sort / MapToSortPartitions / DistributedSort only (tests/sort_checks.py)
+        from tests.dist_checks import _Recompute
+        from tests.sort_checks import run_dist_checks
+        checks = run_dist_checks(api, ctx, rank, world, _Recompute())
+    else:
+        checks = run_checks(api, ctx, rank, world)
 
     ctx.barrier()
     tot = torch.tensor([checks], device="cuda")

@@ -33,3 +33,16 @@ def test_distributed_operators(world, peer):
         pass
     assert p.returncode == 0, p.stdout[-3000:] + "\n" + p.stderr[-6000:]
     assert "DIST_OK world=%d peer=%s" % (world, peer) in p.stdout
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_distributed_sort_over_nccl(world):
+    """DistributedSort / MapToSortPartitions with one process per GPU (the same checks tests/test_gpu_sort.py runs with thread ranks)"""
+    if _ngpus() < world:
+        pytest.skip("needs %d GPUs" % world)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+           "--master-port", str(29600 + world), os.path.join(ROOT, "tests", "dist_worker.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT, env=dict(os.environ, CYLON_TEST_SCOPE="sort"))
+    assert p.returncode == 0, p.stdout[-3000:] + "\n" + p.stderr[-6000:]
+    assert "DIST_OK world=%d" % world in p.stdout
+
