@@ -59,6 +59,18 @@ static int run() {
   std::vector<std::shared_ptr<cylon::Table>> pieces;
   st = cylon::Split(left, 8, pid, pieces);
 
+  // table.hpp:353-404 and partition/partition.hpp:60-74 as cpp/test/partition_test.cpp:81-153 calls them
+  st = cylon::Sort(left, 0, out);
+  st = cylon::Sort(left, 0, out, false);
+  st = cylon::Sort(left, std::vector<int32_t>{0, 1}, out, true);
+  st = cylon::Sort(left, std::vector<int32_t>{0, 1}, out, std::vector<bool>{true, false});
+  st = cylon::DistributedSort(left, 1, out);
+  st = cylon::DistributedSort(left, 0, out, true, {(uint32_t)4, (uint64_t)left->Rows()});
+  st = cylon::DistributedSort(left, {0, 1}, out, {true, false}, {(uint32_t)4, (uint64_t)left->Rows()});
+  std::vector<uint32_t> sort_partitions, sort_count;
+  st = cylon::MapToSortPartitions(left, 0, 4, sort_partitions, sort_count, true, left->Rows(), 4);
+  st = cylon::Split(left, 4, sort_partitions, sort_count, pieces);
+
   std::printf("%lld rows, %d columns, rank %d of %d, retain %d\n", (long long)out->Rows(), out->Columns(), ctx->GetRank(),
               ctx->GetWorldSize(), (int)out->IsRetain());
   out->retainMemory(false);
