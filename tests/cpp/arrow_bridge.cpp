@@ -85,6 +85,40 @@ static int run() {
   bad_hist[0] += 1;
   CHECK(!cylon::Split(t, W, pid, bad_hist, parts5).is_ok());
 
+  // partition_test.cpp:81-103 "range partition test": on a table sorted by the column the target partitions never decrease, the
+  // histogram sums to the row count and Split sizes equal it. partition_test.cpp:105-153 "dist sort test": sorted output, all rows.
+  {
+    std::shared_ptr<cylon::Table> sorted, desc, two;
+    CHECK(cylon::Sort(t, 0, sorted).is_ok());
+    CHECK(sorted->Rows() == n && sorted->get_table()->schema()->Equals(*at->schema()));
+    auto sk = std::static_pointer_cast<arrow::Int64Array>(sorted->get_table()->column(0)->chunk(0));
+    for (int64_t i = 0; i + 1 < n; i++) CHECK(sk->Value(i) <= sk->Value(i + 1));
+    std::vector<uint32_t> spid, scount;
+    CHECK(cylon::MapToSortPartitions(sorted, 0, W, spid, scount, true, sorted->Rows(), W).is_ok());
+    CHECK((int64_t)spid.size() == n && scount.size() == W);
+    for (int64_t i = 0; i + 1 < n; i++) CHECK(spid[i] <= spid[i + 1]);
+    uint64_t stotal = 0;
+    for (uint32_t c : scount) stotal += c;
+    CHECK((int64_t)stotal == n);
+    std::vector<std::shared_ptr<cylon::Table>> sparts;
+    CHECK(cylon::Split(sorted, W, spid, scount, sparts).is_ok());
+    for (uint32_t p = 0; p < W; p++) CHECK(sparts[p]->Rows() == (int64_t)scount[p]);
+    CHECK(cylon::DistributedSort(t, 1, desc, false).is_ok());
+    auto dv = std::static_pointer_cast<arrow::DoubleArray>(desc->get_table()->column(1)->chunk(0));
+    CHECK(desc->Rows() == n);
+    for (int64_t i = 0; i + 1 < n; i++) CHECK(dv->Value(i) >= dv->Value(i + 1));
+    CHECK(cylon::DistributedSort(t, {0, 1}, two, {true, false}, {(uint32_t)W, (uint64_t)t->Rows()}).is_ok());
+    auto k2 = std::static_pointer_cast<arrow::Int64Array>(two->get_table()->column(0)->chunk(0));
+    auto v2 = std::static_pointer_cast<arrow::DoubleArray>(two->get_table()->column(1)->chunk(0));
+    CHECK(two->Rows() == n);
+    for (int64_t i = 0; i + 1 < n; i++) {
+      CHECK(k2->Value(i) <= k2->Value(i + 1));
+      if (k2->Value(i) == k2->Value(i + 1)) CHECK(v2->Value(i) >= v2->Value(i + 1));
+    }
+    std::shared_ptr<cylon::Table> by_string;
+    CHECK(!cylon::Sort(t, 2, by_string).is_ok());  // string sort columns: NotImplemented, not a wrong order
+  }
+
   // a join over Arrow tables end to end: every output row pairs equal keys, and the count is sum cntL * cntR
   auto ar = MakeTable(3000, 400, 2, false);
   std::shared_ptr<cylon::Table> r, joined;
