@@ -4,7 +4,7 @@
 Contract (see DESIGN.md "Measurement"):
   python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun, one rank per GPU)
   python bench.py --impl reference --gpus N --steps K --warmup W
-  python bench.py --config {join,sortjoin,groupby,setops,shuffle} ...     (default join = BASELINE.json configs[1])
+  python bench.py --config {join,sortjoin,groupby,setops,shuffle,sort} ...     (default join = BASELINE.json configs[1])
 
 A "step" is one Distributed* operator over one batch of synthetic input (workloads.py):
   join      cylon::DistributedJoin(inner, HASH), 100M rows per side per GPU, (int64 key, double payload), uniform keys
@@ -12,6 +12,7 @@ A "step" is one Distributed* operator over one batch of synthetic input (workloa
   groupby   cylon::DistributedHashGroupBy(sum, count, min, max), 125M rows per GPU, 1M distinct int64 groups
   setops    cylon::DistributedUnion|Intersect|Subtract / DistributedUnique on (int64, string, double) tables, 25M rows per GPU per table
   shuffle   cylon::Shuffle of an (int64, double) table of --shuffle-bytes per GPU (N = 1: the hash partition + split it starts with)
+  sort      cylon::DistributedSort on the int64 key of an (int64, double) table, 100M rows per GPU (built in round 2, not yet measured)
 `value` = input rows of all ranks / max-over-ranks step time with the inputs already in HBM (CUDA events on the operator's
 stream); `e2e` = the same through host buffers (pinned H2D of the inputs and D2H of the whole result inside the timed
 region). After the timed steps every rank's result is checked (`parity`): the full-size row count against a closed form of
@@ -721,7 +722,97 @@ class ShuffleWorkload(Workload):
                 "sample": "cylon::Shuffle of %d rows per rank on %d ranks (threads, in-memory all-to-all), %.2f s" % (n, world, dt)}
 
 
-WORKLOADS = {w.name: w for w in (JoinWorkload, SortJoinWorkload, GroupByWorkload, SetOpsWorkload, ShuffleWorkload)}
+class SortWorkload(Workload):
+    """cylon::DistributedSort (table.cpp:338-382; SURVEY.md 8f-1): range partition on the key -> shuffle -> local sort."""
+    name = "sort"
+    metric = "DistributedSort input rows/sec"
+    default_rows = 100_000_000
+
+    def host_inputs(self):
+        from cylon_b200 import capi
+        k, v = capi.pinned_array(self.rows, np.int64), capi.pinned_array(self.rows, np.float64)
+        synth_table(self.rows, self.rows * self.world, 9, self.rank, k, v)
+        return [[k, v]]
+
+    def names(self, t):
+        return ["k", "v"]
+
+    def run(self, tables):
+        return tables[0].distributed_sort([0], True)
+
+    def input_rows(self):
+        return self.rows
+
+    def step_algorithmic_bytes(self, out_rows, out_bytes):
+        return self.rows * 16 + out_rows * 16  # every row in once, every row out once
+
+    def workload_text(self):
+        return ("DistributedSort ascending on the int64 key of a %d-row (int64, double) table per GPU, uniform keys in [0, rows*N), "
+                "default SortOptions (1 %% sample, 16 bins per rank)" % self.rows)
+
+    def kernel_bytes(self, kernel, m):
+        # sort_indices: the whole argsort (key in, row order out; its radix passes move 12 B per row each way on top);
+        # gather_fixed: per column, row order in + value in + value out
+        return {"sort_indices": self.rows * 16, "gather_fixed": m * 24, "partition_scatter": self.rows * 32}.get(kernel, 0)
+
+    def parity(self, out_rows_full):
+        env, api = self.env, self.env.api
+        from oracle import pyoracle as orc
+        from oracle import pyref
+        # (1) full size: rows conserved, every rank's keys ascending, and rank r's largest key <= rank r+1's smallest
+        t = api.Table.from_numpy(env.ctx, self.state["host"][0], names=["k", "v"])
+        cs_in = t.checksum()
+        out = t.distributed_sort([0], True)
+        keys = np.asarray(out.to_host()[0]["data"]) if out.row_count else np.zeros(0, np.int64)
+        ascending = bool(np.all(keys[:-1] <= keys[1:])) if len(keys) > 1 else True
+        bounds = env.gather_objects([int(keys[0]), int(keys[-1])] if len(keys) else None)
+        if self.rank == 0:
+            held = [b for b in bounds if b is not None]
+            ascending = ascending and all(a[1] <= b[0] for a, b in zip(held, held[1:]))
+        tot = env.allreduce([out.row_count] + split_checksum(out.checksum()) + split_checksum(cs_in) + [1 if ascending else 0])
+        cs_o = ((tot[1] << 32) + tot[2]) & 0xFFFFFFFFFFFFFFFF
+        cs_i = ((tot[3] << 32) + tot[4]) & 0xFFFFFFFFFFFFFFFF
+        rows_ok = tot[0] == self.rows * self.world and cs_o == cs_i and tot[5] == self.world
+        del out, t, keys
+        # (2) a smaller table per rank with the whole column as the sample (then the reference does not sample at random either):
+        # per-rank row count and checksum against the reference's own DistributedSort on `world` ranks
+        pr = min(self.rows, self.args.parity_rows or 1_000_000)
+        nb = 16 * self.world
+        sk, sv = synth_table(pr, pr * self.world, 19, self.rank)
+        S = api.Table.from_numpy(env.ctx, [sk, sv], names=["k", "v"])
+        so = S.distributed_sort([0], True, nb, pr)
+        sorted_here = bool(np.all(np.diff(np.asarray(so.to_host()[0]["data"])) >= 0)) if so.row_count > 1 else True
+        allr = env.gather_objects([so.row_count, sorted_here] + split_checksum(so.checksum()))
+        ok, checker = True, None
+        if self.rank == 0:
+            tabs = [to_oracle(synth_table(pr, pr * self.world, 19, r), ["k", "v"]) for r in range(self.world)]
+            if pyref.dist_available():
+                exp = pyref.dist_op(pyref.DIST_SORT, tabs, p1=[0], p2=[1], join_type=nb, algorithm=-1)
+                checker = "reference (oracle/_ref cylon::DistributedSort, %d ranks)" % self.world
+            else:
+                exp = orc.distributed_sort(tabs, [0], [True], pr, nb)
+                checker = "oracle (oracle/pyoracle.py)"
+            for r in range(self.world):
+                ok = ok and list(allr[r]) == [exp[r][0].length, True] + split_checksum(orc.table_checksum(exp[r]))
+        ok = bool(env.allreduce([1 if ok else 0], "min")[0])
+        return {"rows_ok": rows_ok, "checksum_ok": ok, "rows": tot[0], "expected_rows": self.rows * self.world,
+                "sample": "full size: rows and checksum conserved, keys ascending within and across ranks; %d rows per rank with the whole "
+                          "column as the sample: per-rank row count + checksum" % pr,
+                "checker": checker}
+
+    def cpu_baseline(self):
+        from oracle import pyref
+        if not pyref.dist_available():
+            return None
+        n = min(self.args.cpu_rows * 2, self.rows)
+        k, v = self.state["host"][0]
+        tab = to_oracle((np.asarray(k[:n]), np.asarray(v[:n])), ["k", "v"])
+        _rows, dt = pyref.dist_op(pyref.DIST_SORT, [tab], p1=[0], p2=[1], rows_only=True)
+        return {"value": n / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+                "sample": "cylon::DistributedSort (= Sort on one rank: std::sort of row indices + arrow Take) of %d rows, %.2f s" % (n, dt)}
+
+
+WORKLOADS = {w.name: w for w in (JoinWorkload, SortJoinWorkload, GroupByWorkload, SetOpsWorkload, ShuffleWorkload, SortWorkload)}
 
 
 # ======================================================================================================== reference arm
@@ -764,6 +855,12 @@ def run_reference(args):
         fallback = lambda: orc.shuffle(tabs, [0])  # noqa: E731
         per_rank_rows, metric = rows, ShuffleWorkload.metric
         text = "Shuffle of an (int64, double) table"
+    elif cfg == "sort":  # whole column as the sample: the reference's own choice of "no sampling" (arrow_partition_kernels.cpp:375-381)
+        tabs = [to_oracle(synth_table(rows, rows * cores, 9, r), ["k", "v"]) for r in range(cores)]
+        call = lambda: pyref.dist_op(pyref.DIST_SORT, tabs, p1=[0], p2=[1], join_type=0, algorithm=-1, rows_only=True)  # noqa: E731
+        fallback = lambda: orc.distributed_sort(tabs, [0], [True], rows, 0)  # noqa: E731
+        per_rank_rows, metric = rows, SortWorkload.metric
+        text = "DistributedSort ascending on the int64 key of an (int64, double) table"
     else:  # setops: the reference's cross-table string comparator reads out of bounds -- the oracle port is timed
         have_ref = False
         op = args.setop
