@@ -31,7 +31,9 @@ int cylon_context_init_threads(const char *group, int32_t rank, int32_t world_si
 int cylon_context_set_stream(cylon_context_t *ctx, void *cuda_stream);
 /* CylonContext::AddConfig (ctx/cylon_context.hpp:85). Keys read by this library: "cylon.join.fused" ("0" = general hash
  * join only), "cylon.shuffle.peer" ("0" = NCCL send/recv instead of NVLink peer stores; must be the same on every rank),
- * "cylon.groupby.fused" / "cylon.setops.fused" ("0" = global row table only). */
+ * "cylon.groupby.fused" / "cylon.setops.fused" ("0" = global row table only), "cylon.groupby.preaggregate" ("0" = raw rows are
+ * shuffled when COUNT is among the aggregates, as the reference does), "cylon.join.overlap" ("1" = DistributedJoin partitions the
+ * arrived left table on the context's second stream while the right table shuffles; same value on every rank). */
 int cylon_context_add_config(cylon_context_t *ctx, const char *key, const char *value);
 int cylon_context_rank(const cylon_context_t *ctx);
 int cylon_context_world_size(const cylon_context_t *ctx);
