@@ -282,3 +282,25 @@ extern "C" int cyl_range_partition(const cyl_column_t *col, int64_t nrows, uint6
   CYL_CUDA(cudaStreamSynchronize(s));  // bin_to_partition is the caller's host memory (pageable: the copy above may still be reading it)
   return CYL_OK;
 }
+
+// bin_to_partition of RangePartitionKernel::build_bin_to_partition (arrow_partition_kernels.cpp:409-427): the histogram's prefix
+// frequency crossing k / num_partitions moves on to the next partition. float_t arithmetic, as there. Host only.
+extern "C" int cyl_range_quantile_split(const uint64_t *global_counts, uint32_t num_bins, uint64_t total_samples, uint32_t num_partitions,
+                                        uint32_t *bin_to_partition) {
+  if (!global_counts || !bin_to_partition) return fail(CYL_Invalid, "cyl_range_quantile_split: null argument");
+  if (num_partitions < 1) return fail(CYL_Invalid, "cyl_range_quantile_split: num_partitions must be positive");
+  const float quantile = (float)(1.0 / num_partitions);
+  float prefix_sum = 0, target_quantile = quantile;
+  uint32_t curr_partition = 0;
+  for (size_t b = 0; b < (size_t)num_bins + 2; b++) {
+    bin_to_partition[b] = curr_partition;
+    const float freq = total_samples ? (float)global_counts[b] / (float)total_samples : 0.0f;
+    prefix_sum += freq;
+    if (prefix_sum > target_quantile) {
+      curr_partition += (curr_partition < num_partitions - 1);
+      target_quantile += quantile;
+    }
+  }
+  return CYL_OK;
+}
+

@@ -20,26 +20,6 @@ namespace {
 
 using detail::DevBuf;
 
-// bin_to_partition of RangePartitionKernel::build_bin_to_partition (arrow_partition_kernels.cpp:409-427): the histogram's prefix
-// frequency crossing k / num_partitions moves on to the next partition. float_t arithmetic, as there.
-std::vector<uint32_t> QuantileSplit(const std::vector<uint64_t> &global_counts, uint64_t total_samples, uint32_t num_partitions) {
-  std::vector<uint32_t> bin_to_partition;
-  bin_to_partition.reserve(global_counts.size());
-  const float quantile = (float)(1.0 / num_partitions);
-  float prefix_sum = 0, target_quantile = quantile;
-  uint32_t curr_partition = 0;
-  for (uint64_t c : global_counts) {
-    bin_to_partition.push_back(curr_partition);
-    const float freq = total_samples ? (float)c / (float)total_samples : 0.0f;
-    prefix_sum += freq;
-    if (prefix_sum > target_quantile) {
-      curr_partition += (curr_partition < num_partitions - 1);
-      target_quantile += quantile;
-    }
-  }
-  return bin_to_partition;
-}
-
 Status CheckSortColumn(const Table &t, int32_t col, const char *who) {
   RETURN_CYLON_STATUS_IF_FAILED(detail::CheckColumns(t, {col}, who));
   const auto &c = t.GetColumn(col);
@@ -92,7 +72,8 @@ Status RangePartitionIds(const std::shared_ptr<Table> &table, int32_t column_idx
         for (size_t b = 0; b < bins; b++) counts[b] += (uint64_t)all[(size_t)r * bins + b];
     }
   }
-  const std::vector<uint32_t> bin_to_partition = QuantileSplit(counts, (uint64_t)total_sampled, num_partitions);
+  std::vector<uint32_t> bin_to_partition(bins, 0);  // quantile split of the bins, in float like the reference (:409-427)
+  CYL_RETURN_IF_FAILED(cyl_range_quantile_split(counts.data(), num_bins, (uint64_t)total_sampled, num_partitions, bin_to_partition.data()));
   CYL_RETURN_IF_FAILED(cyl_range_partition(&col, n, min_key, max_key, total_sampled, num_bins, bin_to_partition.data(), num_partitions, ascending ? 1 : 0,
                                            pid, partition_hist, stream));
   return Status::OK();

@@ -323,7 +323,10 @@ int cyl_sort_indices(const cyl_column_t *keys /* host array */, int32_t nkeys, c
  *      column's own C++ type as the reference's template does (host out, to be summed over the ranks).
  *   3. cyl_range_partition: target partition of EVERY row, bin_to_partition[get_bin_pos(value)] (num_partitions - 1 - that
  *      when descending), and the rows per partition. total_samples <= 0 (nothing sampled on any rank) sends every row to bin 0.
- * All three synchronise. */
+ * All three synchronise. Between 2 and 3, cyl_range_quantile_split (host-only arithmetic, no GPU needed) turns the summed histogram
+ * into bin_to_partition as build_bin_to_partition does (:409-427, float_t prefix frequencies against k / num_partitions). */
+int cyl_range_quantile_split(const uint64_t *global_counts /* host, num_bins + 2 */, uint32_t num_bins, uint64_t total_samples, uint32_t num_partitions,
+                             uint32_t *bin_to_partition /* host out, num_bins + 2 */);
 int cyl_range_sample_minmax(const cyl_column_t *col, int64_t nrows, int64_t num_samples, uint64_t *min_key /* host out */,
                             uint64_t *max_key /* host out */, int64_t *count /* host out */, void *stream);
 int cyl_range_sample_histogram(const cyl_column_t *col, int64_t nrows, int64_t num_samples, uint64_t min_key, uint64_t max_key, uint32_t num_bins,

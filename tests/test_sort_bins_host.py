@@ -78,3 +78,33 @@ def test_bin_positions_match_oracle(host, kind):
             exp = orc.sort_bin_pos(v, mn, mx, nb)
             bad = np.nonzero(out.astype(np.int64) != exp)[0]
             assert len(bad) == 0, (kind, trial, nb, v[bad[:3]], out[bad[:3]], exp[bad[:3]], mn, mx)
+
+
+def test_quantile_split_matches_oracle():
+    """cyl_range_quantile_split (host-only entry point of the library) against the oracle's float restatement of
+    build_bin_to_partition, on random, skewed, empty and single-bin histograms"""
+    so = os.path.join(ROOT, "cylon_b200", "lib", "libcylon_b200.so")
+    if not os.path.exists(so):
+        pytest.skip("library not built")
+    lib = C.CDLL(so)
+    rng = np.random.default_rng(3)
+    for trial in range(300):
+        nb = int(rng.choice([1, 2, 7, 16, 64, 128, 1000]))
+        parts = int(rng.choice([1, 2, 3, 4, 8, 13, 64]))
+        kind = trial % 4
+        if kind == 0:
+            counts = rng.integers(0, 1000, nb + 2)
+        elif kind == 1:
+            counts = (rng.pareto(1.2, nb + 2) * 50).astype(np.int64)
+        elif kind == 2:
+            counts = np.zeros(nb + 2, dtype=np.int64)
+            counts[rng.integers(0, nb + 2)] = 12345
+        else:
+            counts = np.zeros(nb + 2, dtype=np.int64)
+        counts = counts.astype(np.uint64)
+        total = int(counts.sum()) if trial % 5 else int(counts.sum()) + 17  # the reference's total need not equal the sum
+        out = np.zeros(nb + 2, dtype=np.uint32)
+        rc = lib.cyl_range_quantile_split(counts.ctypes.data_as(C.c_void_p), C.c_uint32(nb), C.c_uint64(total), C.c_uint32(parts),
+                                          out.ctypes.data_as(C.c_void_p))
+        assert rc == 0
+        assert np.array_equal(out, orc.sort_bin_to_partition(counts, total, parts)), (nb, parts, kind)
